@@ -1,0 +1,186 @@
+"""PNL-v2 -- the packed node list the device reads (spec: DESIGN.md "Data layout").
+
+One byte stream plus one offset column; every string the reference looks at is kept whole, so
+key matching, quantity parsing and the Ready test all happen on the device, not in the packer.
+
+    rows    u8[T]      node rows back to back; node i is rows[row_ptr[i] : row_ptr[i+1]]
+    row_ptr u32[N+1]   row_ptr[0] == 0 (or the shard's first byte), non-decreasing
+
+    row   := cap_len:u16le [cap_len32:u32le if cap_len == 0xFFFF]
+             entry*  (exactly cap_len bytes: the node's status.capacity, in dict order)
+             entry*  (rest of the row: the node's status.conditions, as (type, status))
+    entry := klen:u8 vlen:u8 [klen32:u32le if klen == 255] [vlen32:u32le if vlen == 255]
+             key[klen] value[vlen]          (UTF-8, 'surrogatepass')
+
+Marshalling done here (type adaptation only, no classification):
+  * `status` falsy or `status.capacity` falsy -> no capacity entries (check-gpu-node.py:183-185)
+  * a capacity value that is not a `str` becomes `""` when falsy (the reference skips it, :188)
+    and `str(value)` otherwise (the reference applies `str` itself, :192)
+  * list elements that are not `V1NodeCondition` instances are left out: the reference's
+    `isinstance` test (:176) can never accept them; a non-`str` type/status is stored as `""`
+Device buffers must be 16-byte aligned with `rows` padded by >= 32 bytes and `row_ptr` by
+>= 4 entries past their last valid element (bulk copies move whole 16-byte units).
+"""
+from __future__ import annotations
+
+import struct
+from dataclasses import dataclass
+from typing import Any, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+GPU_RESOURCE_KEYS = ("nvidia.com/gpu", "amd.com/gpu", "gpu.intel.com/i915", "intel.com/gpu")
+
+ROWS_PAD = 32        # bytes readable past T
+ROWPTR_PAD = 4       # entries readable past N+1
+
+
+def _utf8(s: str) -> bytes:
+    return s.encode("utf-8", "surrogatepass")
+
+
+def encode_entry(key: bytes, value: bytes) -> bytes:
+    kl, vl = len(key), len(value)
+    head = bytes((min(kl, 255), min(vl, 255)))
+    if kl >= 255:
+        head += struct.pack("<I", kl)
+    if vl >= 255:
+        head += struct.pack("<I", vl)
+    return head + key + value
+
+
+def marshal_quantity(value: Any) -> bytes:
+    """Bytes the device parses for one capacity value (see module docstring)."""
+    if isinstance(value, str):
+        return _utf8(value)
+    try:
+        return b"" if not value else _utf8(str(value))
+    except Exception:
+        return b"?"          # `str()` raised inside the reference's try block -> key dropped
+
+
+def encode_row(capacity: Optional[Iterable[Tuple[Any, Any]]],
+               conditions: Optional[Iterable[Tuple[Any, Any]]]) -> bytes:
+    """One row from (key, value) pairs and (type, status) pairs."""
+    cap = bytearray()
+    for k, v in capacity or ():
+        if not isinstance(k, str):
+            continue                      # cannot equal any of the four str keys
+        cap += encode_entry(_utf8(k), marshal_quantity(v))
+    out = bytearray()
+    if len(cap) >= 0xFFFF:
+        out += b"\xff\xff" + struct.pack("<I", len(cap))
+    else:
+        out += struct.pack("<H", len(cap))
+    out += cap
+    for t, s in conditions or ():
+        out += encode_entry(_utf8(t) if isinstance(t, str) else b"",
+                            _utf8(s) if isinstance(s, str) else b"")
+    return bytes(out)
+
+
+def _condition_class():
+    try:
+        from kubernetes.client import V1NodeCondition
+    except ImportError as e:          # no silent stand-in: V1Node objects imply the client is there
+        raise ImportError("packing V1Node objects needs `kubernetes.client.V1NodeCondition`") from e
+    return V1NodeCondition
+
+
+def node_row(node: Any, cond_cls=None) -> bytes:
+    """Row for one V1Node-like object (attribute names of check-gpu-node.py:173-187)."""
+    cond_cls = cond_cls or _condition_class()
+    st = node.status
+    if not st:
+        return b"\x00\x00"
+    cap = st.capacity.items() if st.capacity else None
+    conds = None
+    if st.conditions:
+        conds = [(c.type, c.status) for c in st.conditions if isinstance(c, cond_cls)]
+    return encode_row(cap, conds)
+
+
+@dataclass
+class PackedNodeList:
+    rows: np.ndarray        # uint8, length T + ROWS_PAD (zero padded)
+    row_ptr: np.ndarray     # uint32, length N + 1 + ROWPTR_PAD (padding repeats T)
+    n_nodes: int
+
+    @property
+    def n_bytes(self) -> int:
+        return int(self.row_ptr[self.n_nodes])
+
+    def row(self, i: int) -> bytes:
+        return self.rows[int(self.row_ptr[i]):int(self.row_ptr[i + 1])].tobytes()
+
+    def slice(self, lo: int, hi: int) -> "PackedNodeList":
+        """Nodes [lo, hi) as a self-contained list (offsets rebased) -- one rank's shard."""
+        b0, b1 = int(self.row_ptr[lo]), int(self.row_ptr[hi])
+        return from_parts(self.rows[b0:b1], self.row_ptr[lo:hi + 1].astype(np.int64) - b0)
+
+
+def from_parts(rows: np.ndarray, row_ptr: np.ndarray) -> PackedNodeList:
+    n = len(row_ptr) - 1
+    t = int(row_ptr[n]) if n >= 0 else 0
+    if t >= 2 ** 32 - ROWS_PAD:
+        raise ValueError("PNL-v2 rows are limited to 4 GiB per list; split the fleet")
+    r = np.zeros(t + ROWS_PAD, dtype=np.uint8)
+    r[:t] = rows[:t]
+    p = np.full(n + 1 + ROWPTR_PAD, t, dtype=np.uint32)
+    p[:n + 1] = row_ptr
+    return PackedNodeList(r, p, n)
+
+
+def from_rows(rows: Sequence[bytes]) -> PackedNodeList:
+    lens = np.fromiter((len(r) for r in rows), dtype=np.int64, count=len(rows))
+    ptr = np.zeros(len(rows) + 1, dtype=np.int64)
+    np.cumsum(lens, out=ptr[1:])
+    return from_parts(np.frombuffer(b"".join(rows), dtype=np.uint8), ptr)
+
+
+def pack_nodes(nodes: Optional[Iterable[Any]]) -> PackedNodeList:
+    """V1Node objects (what `api.list_node().items` holds) -> PNL-v2."""
+    cls = _condition_class()
+    return from_rows([node_row(n, cls) for n in (nodes or ())])
+
+
+# ---------------------------------------------------------------------------------------------
+# Reading rows back (for the host side of the bignum escape and for tests).
+# ---------------------------------------------------------------------------------------------
+def _entries(buf: bytes, pos: int, end: int) -> List[Tuple[bytes, bytes, int]]:
+    """[(key, value, value_offset)] of the entries in buf[pos:end]; stops at a malformed entry."""
+    out = []
+    while pos + 2 <= end:
+        kl, vl = buf[pos], buf[pos + 1]
+        pos += 2
+        if kl == 255:
+            if pos + 4 > end:
+                break
+            kl = struct.unpack_from("<I", buf, pos)[0]
+            pos += 4
+        if vl == 255:
+            if pos + 4 > end:
+                break
+            vl = struct.unpack_from("<I", buf, pos)[0]
+            pos += 4
+        if pos + kl + vl > end:
+            break
+        out.append((buf[pos:pos + kl], buf[pos + kl:pos + kl + vl], pos + kl))
+        pos += kl + vl
+    return out
+
+
+def decode_row(row: bytes) -> Tuple[List[Tuple[bytes, bytes]], List[Tuple[bytes, bytes]]]:
+    """(capacity entries, condition entries) of one row, as raw byte pairs."""
+    if len(row) < 2:
+        return [], []
+    cap_len, pos = struct.unpack_from("<H", row, 0)[0], 2
+    if cap_len == 0xFFFF:
+        if len(row) < 6:
+            return [], []
+        cap_len, pos = struct.unpack_from("<I", row, 2)[0], 6
+    if pos + cap_len > len(row):
+        return [], []
+    caps = [(k, v) for k, v, _ in _entries(row, pos, pos + cap_len)]
+    conds = [(k, v) for k, v, _ in _entries(row, pos + cap_len, len(row))]
+    return caps, conds
