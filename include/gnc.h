@@ -1,0 +1,137 @@
+/* gnc.h -- C ABI of libgnc.so, the B200 (sm_100a) node-classification library.
+ *
+ * The reference (ahaljh/k8s-gpu-node-checker) exposes no FFI: its seam for this path is the Python
+ * function list_gpu_nodes(api) (check-gpu-node.py:215-226).  The entry points below are what a
+ * binding for that function needs: one call that classifies a packed node list on the device and
+ * one that combines the ranks of a sharded fleet.  Each comment names the reference lines the
+ * call replaces.  No exceptions cross the boundary; every call returns 0 or a negative gnc_status
+ * and leaves the text in gnc_last_error().  A context belongs to one GPU and one caller thread at a
+ * time; distinct contexts are independent.
+ *
+ * Input format: PNL-v2 (DESIGN.md "Data layout"; packer in k8s-gpu-node-checker_b200/pnl.py).
+ */
+#ifndef GNC_H_
+#define GNC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GNC_ABI_VERSION 2
+
+typedef struct gnc_ctx gnc_ctx;
+
+typedef enum gnc_status {
+  GNC_OK = 0,
+  GNC_ERR_ARG = -1,      /* null / misaligned pointer, size out of range */
+  GNC_ERR_CUDA = -2,     /* a CUDA runtime call failed; text has the CUDA error */
+  GNC_ERR_NOMEM = -3,
+  GNC_ERR_STATE = -4,    /* call not valid for this context (e.g. gather without a communicator) */
+  GNC_ERR_COMM = -5,     /* NCCL failure */
+  GNC_ERR_OVERFLOW = -6  /* an output table was too small; counts say by how much */
+} gnc_status;
+
+/* Per-node flag bits written to gnc_result.flags. */
+#define GNC_F_GPU 0x01u       /* gpus > 0: the node is in gpu_nodes          (check-gpu-node.py:222) */
+#define GNC_F_READY 0x02u     /* is_ready(node)                                (check-gpu-node.py:172-178) */
+#define GNC_F_DEFERRED 0x04u  /* a kept value needs > 18 digits: see gnc_defer_rec; GNC_F_GPU not decided */
+#define GNC_F_KEY0 0x08u      /* bits 3..6: key k of GPU_RESOURCE_KEYS is in gpu_breakdown (:186-195) */
+#define GNC_F_MALFORMED 0x80u /* the row's own lengths did not fit the row; the rest of it was ignored */
+
+/* Slots of the counts block (int64[GNC_N_COUNTS]). */
+enum {
+  GNC_C_GPU_NODES = 0,   /* len(gpu_nodes)        before deferred nodes are added (check-gpu-node.py:275) */
+  GNC_C_READY_NODES = 1, /* len(ready_gpu_nodes)  likewise                         (check-gpu-node.py:276) */
+  GNC_C_DEFERRED = 2,    /* nodes with GNC_F_DEFERRED */
+  GNC_C_SCANNED = 3,     /* nodes classified */
+  GNC_C_KEY_LO = 4,      /* [4..7]  per-key GPU totals over the GPU nodes, low 64 bits            */
+  GNC_C_KEY_HI = 8,      /* [8..11] high 64 bits (two's-complement 128-bit; exact for any fleet)  */
+  GNC_C_MALFORMED = 12,
+  GNC_C_DEFER_DROPPED = 13, /* deferred nodes that did not fit gnc_result.defer_cap */
+  GNC_C_OUT_DROPPED = 14,   /* GPU nodes that did not fit gnc_result.out_cap */
+  GNC_N_COUNTS = 16
+};
+
+/* One packed shard, DEVICE pointers.  rows and row_ptr must be 16-byte aligned, rows readable for
+ * rows_bytes + 32 bytes and row_ptr for n_nodes + 1 + 4 entries (bulk copies move 16-byte units). */
+typedef struct gnc_batch {
+  const uint8_t* rows;     /* node rows, back to back */
+  const uint32_t* row_ptr; /* n_nodes + 1 byte offsets into rows */
+  uint64_t rows_bytes;     /* row_ptr[n_nodes] */
+  uint32_t n_nodes;
+  uint32_t node_base;      /* fleet index of this shard's node 0; added to every index written */
+} gnc_batch;
+
+/* A node whose value texts the caller must add up with wider integers: off/len locate the value of
+ * key k inside gnc_batch.rows (off == 0xFFFFFFFF: key not kept). Texts already passed the grammar. */
+typedef struct gnc_defer_rec {
+  uint32_t node;
+  uint32_t off[4];
+  uint32_t len[4];
+} gnc_defer_rec;
+
+/* Caller-allocated DEVICE outputs.  gpu_* hold one record per GPU node, in fleet order. */
+typedef struct gnc_result {
+  uint8_t* flags;        /* [n_nodes] */
+  uint32_t* gpu_idx;     /* [out_cap]     node index (node_base + i) of each GPU node, ascending */
+  int64_t* gpu_total;    /* [out_cap]     "gpus"           (check-gpu-node.py:201) */
+  int64_t* gpu_vals;     /* [out_cap][4]  "gpu_breakdown" values in GPU_RESOURCE_KEYS order, 0 if absent; 16-byte aligned */
+  gnc_defer_rec* defer;  /* [defer_cap]   unordered */
+  int64_t* counts;       /* [GNC_N_COUNTS] */
+  uint32_t out_cap;      /* n_nodes is always enough */
+  uint32_t defer_cap;
+} gnc_result;
+
+/* ABI version of the loaded library (compare with GNC_ABI_VERSION). */
+int gnc_abi_version(void);
+
+/* Create the context for CUDA device `device` as rank `rank` of `world`.  For world > 1 pass the
+ * ncclUniqueId bytes rank 0 obtained from gnc_comm_id(); for world == 1 pass NULL/0.
+ * Stands where the reference builds its client (check-gpu-node.py:253): one per process. */
+int gnc_create(gnc_ctx** out, int device, int rank, int world, const void* nccl_id, size_t nccl_id_len);
+
+/* Fill `id` (at least 128 bytes) with a fresh ncclUniqueId; returns its length in *len. */
+int gnc_comm_id(void* id, size_t cap, size_t* len);
+
+/* Size the library's scratch for shards of up to max_nodes nodes now, so that gnc_classify never
+ * allocates (it otherwise grows the scratch on demand, which synchronises the device). */
+int gnc_reserve(gnc_ctx*, uint32_t max_nodes);
+
+/* CPython's int() refuses more than this many digit characters (sys.get_int_max_str_digits(),
+ * default 4300; 0 = no limit).  Default 4300. */
+int gnc_set_max_str_digits(gnc_ctx*, int max_digits);
+
+/* Classify one shard: the loop of list_gpu_nodes (check-gpu-node.py:220-225) with gpu_capacity
+ * (:181-196), is_ready (:172-178) and the gpus sum (:201) per node, the ordered gpu_nodes filter
+ * (:222-223) and the counts one_shot derives (:275-276).  Work is enqueued on `cuda_stream`
+ * (a cudaStream_t, NULL = default stream); the call does not wait for it. */
+int gnc_classify(gnc_ctx*, const gnc_batch* in, const gnc_result* out, void* cuda_stream);
+
+/* Combine the ranks of a sharded fleet (no-op for world == 1): all-reduce of counts, then an
+ * all-gather of every rank's gpu_idx/gpu_total/gpu_vals into `all` at rank-ordered offsets, which
+ * reproduces the reference's single ordered list (check-gpu-node.py:220-225).  `local` is this
+ * rank's gnc_classify result; `all` must hold the fleet-wide GPU-node count. */
+int gnc_gather(gnc_ctx*, const gnc_result* local, const gnc_result* all, void* cuda_stream);
+
+/* Same classification from HOST memory: copies the shard to the device in pipelined chunks,
+ * classifies, and copies flags / GPU-node records / counts back to the caller's HOST buffers
+ * (the gnc_batch / gnc_result pointers are host pointers here).  Blocks until the results are in
+ * host memory.  This is the call a binding without device buffers of its own uses. */
+int gnc_classify_host(gnc_ctx*, const gnc_batch* host_in, const gnc_result* host_out);
+
+/* Kernels this context has launched since it was created (for benchmark accounting). */
+uint64_t gnc_launch_count(const gnc_ctx*);
+
+/* Unicode tables the quantity parser was built with (decimal-digit run starts, wide spaces). */
+int gnc_unicode_tables(const uint32_t** nd_runs, int* n_runs, const uint32_t** spaces, int* n_spaces);
+
+const char* gnc_last_error(const gnc_ctx*);
+void gnc_destroy(gnc_ctx*);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNC_H_ */

@@ -1,0 +1,81 @@
+"""Drop-in for the reference's classification seam.
+
+`list_gpu_nodes(api)` has the signature and return value of check-gpu-node.py:215-226: two lists of
+six-key dicts (`name, ready, gpus, gpu_breakdown, labels, taints`, :202-212), GPU nodes in API order,
+the Ready list holding the same dict objects.  The per-node decisions come from the B200 kernels;
+this module only packs the nodes and dresses the winners with their pass-through payload.
+"""
+from __future__ import annotations
+
+import json
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import engine, pnl
+
+_default: Optional[engine.Classifier] = None
+
+
+def default_classifier() -> engine.Classifier:
+    global _default
+    if _default is None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("no CUDA device: the classification path runs on the GPU only (no CPU fallback)")
+        _default = engine.Classifier(torch.cuda.current_device())
+    return _default
+
+
+def classify_packed(p: pnl.PackedNodeList, clf: Optional[engine.Classifier] = None) -> engine.FleetResult:
+    """Host-resident PNL-v2 -> FleetResult through the host-buffer entry point (gnc_classify_host)."""
+    clf = clf or default_classifier()
+    out = clf.classify_host(p)
+    return engine.finish(out["flags"][:p.n_nodes], out["gpu_idx"], out["gpu_total"], out["gpu_vals"], out["counts"],
+                         out["defer"], p.rows)
+
+
+def _payload(node: Any) -> Tuple[str, Dict, List]:
+    """name / labels / taints exactly as check-gpu-node.py:203, :207-211 builds them."""
+    md, spec = node.metadata, node.spec
+    taints = [{"key": t.key, "value": t.value, "effect": t.effect} for t in (spec.taints or [])] \
+        if spec and getattr(spec, "taints", None) else []
+    return (md.name if md else ""), (md.labels if md and md.labels else {}), taints
+
+
+def build_records(nodes: Sequence[Any], res: engine.FleetResult) -> Tuple[List[Dict], List[Dict]]:
+    """(gpu_nodes, ready_gpu_nodes) from the device's decisions plus each node's payload."""
+    gpu_nodes: List[Dict] = []
+    ready_nodes: List[Dict] = []
+    for pos, i in enumerate(res.gpu_idx.tolist()):
+        name, labels, taints = _payload(nodes[i])
+        rec = {"name": name, "ready": res.is_ready(pos), "gpus": res.gpu_total[pos],
+               "gpu_breakdown": res.breakdown(pos), "labels": labels, "taints": taints}
+        gpu_nodes.append(rec)
+        if rec["ready"]:
+            ready_nodes.append(rec)
+    return gpu_nodes, ready_nodes
+
+
+def classify_nodes(nodes: Optional[Sequence[Any]], clf: Optional[engine.Classifier] = None):
+    nodes = list(nodes or [])
+    res = classify_packed(pnl.pack_nodes(nodes), clf)
+    return build_records(nodes, res)
+
+
+def list_gpu_nodes(api, clf: Optional[engine.Classifier] = None) -> Tuple[List[Dict], List[Dict]]:
+    """Returns (gpu_nodes, ready_gpu_nodes) as list of dicts -- check-gpu-node.py:215-226."""
+    return classify_nodes(api.list_node().items or [], clf)
+
+
+def summary_json(gpu_nodes: List[Dict], ready_gpu_nodes: List[Dict]) -> str:
+    """The `--json` document (check-gpu-node.py:274-279)."""
+    return json.dumps({"total_nodes": len(gpu_nodes), "ready_nodes": len(ready_gpu_nodes), "nodes": gpu_nodes},
+                      ensure_ascii=False, indent=2)
+
+
+def exit_code(gpu_nodes: List[Dict], ready_gpu_nodes: List[Dict]) -> int:
+    """check-gpu-node.py:289-293."""
+    if ready_gpu_nodes:
+        return 0
+    return 3 if gpu_nodes else 2

@@ -1,0 +1,578 @@
+// gnc.cu -- C ABI of libgnc.so (include/gnc.h): contexts, launch logic, host-buffer path, gather.
+//
+// No torch types, no exceptions across the boundary.  Device code is in classify.cuh.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "classify.cuh"
+
+using gnc::Params;
+using gnc::ScratchHeader;
+
+namespace {
+
+// ---- kernel variants: nodes per tile x pipeline depth x bytes per stage x CTAs per SM ------------
+struct Variant {
+  const char* name;
+  int tile_nodes, stage_bytes, threads;
+  size_t smem;
+  const void* fn;
+  void (*launch)(const Params&, int grid, size_t smem, cudaStream_t);
+};
+
+template <int TN, int ST, int SB, int MC>
+void launch_variant(const Params& p, int grid, size_t smem, cudaStream_t stream) {
+  gnc::classify_kernel<TN, ST, SB, MC><<<grid, 2 * TN + 32, smem, stream>>>(p);
+}
+template <int TN, int ST, int SB, int MC>
+Variant make_variant(const char* name) {
+  return Variant{name, TN, SB, 2 * TN + 32, sizeof(gnc::Smem<TN, ST, SB>),
+                 (const void*)gnc::classify_kernel<TN, ST, SB, MC>, launch_variant<TN, ST, SB, MC>};
+}
+
+// Ordered by preference: the first whose stage holds an average tile with 6 % to spare is used.
+const Variant kVariants[] = {
+    make_variant<256, 2, 56320, 2>("t256s2"),
+    make_variant<128, 3, 36864, 2>("t128s3"),
+    make_variant<128, 2, 56320, 2>("t128s2"),
+    make_variant<64, 2, 56320, 2>("t64s2"),
+    make_variant<32, 2, 56320, 2>("t32s2"),
+};
+constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+
+}  // namespace
+
+struct gnc_ctx {
+  int device = 0, rank = 0, world = 1;
+  int sm_count = 0;
+  int max_digits = 4300;
+  uint32_t epoch = 0;
+  uint64_t launches = 0;
+  int forced_variant = -1;
+  int ctas_per_sm[kNumVariants] = {};
+  // scratch: header + tile states
+  void* scratch = nullptr;
+  size_t scratch_tiles = 0;
+  // host-buffer path staging
+  struct HostStage {
+    uint8_t* d_rows = nullptr;
+    uint32_t* d_row_ptr = nullptr;
+    uint8_t* d_flags = nullptr;
+    uint32_t* d_idx = nullptr;
+    int64_t* d_total = nullptr;
+    int64_t* d_vals = nullptr;
+    gnc_defer_rec* d_defer = nullptr;
+    int64_t* d_counts = nullptr;
+    int64_t* h_counts = nullptr;  // pinned
+    size_t rows_cap = 0, nodes_cap = 0, defer_cap = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;    // counts are in h_counts
+    cudaEvent_t kernel = nullptr;  // this stage's kernel has finished with the shared scratch
+  } hs[2];
+  // NCCL (resolved at run time from the already-loaded libnccl.so.2)
+  void* nccl_lib = nullptr;
+  void* comm = nullptr;
+  int64_t* d_all_counts = nullptr;  // [world][GNC_N_COUNTS]
+  int64_t* h_all_counts = nullptr;  // pinned
+  std::string err;
+};
+
+namespace {
+
+int comm_init(gnc_ctx* c, const void* id, size_t id_len);
+void comm_destroy(gnc_ctx* c);
+
+int fail(gnc_ctx* c, int code, const std::string& msg) {
+  if (c) c->err = msg;
+  return code;
+}
+#define CUDA_TRY(c, expr)                                                                         \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(c, GNC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorName(e_) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+uint32_t tiles_for(uint32_t n_nodes, int tile_nodes) { return (n_nodes + tile_nodes - 1) / tile_nodes; }
+
+int ensure_scratch(gnc_ctx* c, size_t tiles) {
+  if (c->scratch && tiles <= c->scratch_tiles) return GNC_OK;
+  size_t want = std::max<size_t>(tiles, 4096);
+  if (c->scratch) {
+    CUDA_TRY(c, cudaDeviceSynchronize());
+    CUDA_TRY(c, cudaFree(c->scratch));
+    c->scratch = nullptr;
+    c->scratch_tiles = 0;
+  }
+  size_t bytes = sizeof(ScratchHeader) + want * sizeof(unsigned long long);
+  CUDA_TRY(c, cudaMalloc(&c->scratch, bytes));
+  CUDA_TRY(c, cudaMemset(c->scratch, 0, bytes));
+  CUDA_TRY(c, cudaDeviceSynchronize());
+  c->scratch_tiles = want;
+  return GNC_OK;
+}
+
+int pick_variant(const gnc_ctx* c, uint64_t rows_bytes, uint32_t n_nodes) {
+  if (c->forced_variant >= 0) return c->forced_variant;
+  const double avg = n_nodes ? (double)rows_bytes / n_nodes : 0.0;
+  for (int v = 0; v < kNumVariants; v++)
+    if (avg * kVariants[v].tile_nodes * 1.06 + 32 <= kVariants[v].stage_bytes) return v;
+  return kNumVariants - 1;  // tiles that do not fit are read straight from global memory
+}
+
+bool aligned16(const void* p) { return ((uintptr_t)p & 15u) == 0; }
+
+int check_batch(gnc_ctx* c, const gnc_batch* in, const gnc_result* out) {
+  if (!in || !out) return fail(c, GNC_ERR_ARG, "null batch or result");
+  if (!out->counts) return fail(c, GNC_ERR_ARG, "result.counts is null");
+  if (in->n_nodes) {
+    if (!in->rows || !in->row_ptr) return fail(c, GNC_ERR_ARG, "batch.rows / batch.row_ptr is null");
+    if (!aligned16(in->rows) || !aligned16(in->row_ptr))
+      return fail(c, GNC_ERR_ARG, "batch.rows and batch.row_ptr must be 16-byte aligned");
+    if (in->rows_bytes > 0xFFFFFFFFull - 64) return fail(c, GNC_ERR_ARG, "rows_bytes exceeds the 4 GiB PNL-v2 limit");
+    if (!out->flags || !out->gpu_idx || !out->gpu_total || !out->gpu_vals)
+      return fail(c, GNC_ERR_ARG, "result.flags / gpu_idx / gpu_total / gpu_vals is null");
+    if (!aligned16(out->gpu_vals)) return fail(c, GNC_ERR_ARG, "result.gpu_vals must be 16-byte aligned");
+    if ((uint64_t)in->node_base + in->n_nodes > 0x100000000ull)
+      return fail(c, GNC_ERR_ARG, "node_base + n_nodes exceeds 2^32");
+    if (out->defer_cap && !out->defer) return fail(c, GNC_ERR_ARG, "result.defer is null but defer_cap > 0");
+  }
+  return GNC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gnc_abi_version(void) { return GNC_ABI_VERSION; }
+
+int gnc_create(gnc_ctx** out, int device, int rank, int world, const void* nccl_id, size_t nccl_id_len) {
+  if (!out) return GNC_ERR_ARG;
+  *out = nullptr;
+  gnc_ctx* c = new (std::nothrow) gnc_ctx();
+  if (!c) return GNC_ERR_NOMEM;
+  *out = c;  // returned even on failure so the caller can read gnc_last_error, then gnc_destroy
+  c->device = device;
+  c->rank = rank;
+  c->world = world < 1 ? 1 : world;
+  if (rank < 0 || rank >= c->world) return fail(c, GNC_ERR_ARG, "rank outside [0, world)");
+  CUDA_TRY(c, cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(c, cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return fail(c, GNC_ERR_STATE, std::string("libgnc is built for sm_100a (B200); device is ") + prop.name);
+  c->sm_count = prop.multiProcessorCount;
+  for (int v = 0; v < kNumVariants; v++) {
+    CUDA_TRY(c, cudaFuncSetAttribute(kVariants[v].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVariants[v].smem));
+    int n = 0;
+    CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kVariants[v].fn, kVariants[v].threads, kVariants[v].smem));
+    if (n < 1) return fail(c, GNC_ERR_STATE, std::string("kernel variant does not fit an SM: ") + kVariants[v].name);
+    c->ctas_per_sm[v] = n;
+  }
+  if (const char* f = getenv("GNC_VARIANT")) {
+    for (int v = 0; v < kNumVariants; v++)
+      if (!strcmp(f, kVariants[v].name)) c->forced_variant = v;
+    if (c->forced_variant < 0) return fail(c, GNC_ERR_ARG, std::string("GNC_VARIANT names no kernel variant: ") + f);
+  }
+  int rc = ensure_scratch(c, 1 << 16);
+  if (rc) return rc;
+  if (c->world > 1) {
+    rc = comm_init(c, nccl_id, nccl_id_len);
+    if (rc) return rc;
+  }
+  return GNC_OK;
+}
+
+int gnc_reserve(gnc_ctx* c, uint32_t max_nodes) {
+  if (!c) return GNC_ERR_ARG;
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  return ensure_scratch(c, tiles_for(max_nodes, kVariants[kNumVariants - 1].tile_nodes));
+}
+
+int gnc_set_max_str_digits(gnc_ctx* c, int max_digits) {
+  if (!c || max_digits < 0) return GNC_ERR_ARG;
+  c->max_digits = max_digits;
+  return GNC_OK;
+}
+
+int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* cuda_stream) {
+  if (!c) return GNC_ERR_ARG;
+  int rc = check_batch(c, in, out);
+  if (rc) return rc;
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  if (in->n_nodes == 0) {
+    CUDA_TRY(c, cudaMemsetAsync(out->counts, 0, GNC_N_COUNTS * sizeof(int64_t), stream));
+    return GNC_OK;
+  }
+  const int v = pick_variant(c, in->rows_bytes, in->n_nodes);
+  const Variant& var = kVariants[v];
+  const uint32_t tiles = tiles_for(in->n_nodes, var.tile_nodes);
+  rc = ensure_scratch(c, tiles);
+  if (rc) return rc;
+  c->epoch = (c->epoch + 1) & gnc::kEpochMask;
+  if (c->epoch == 0) {  // epoch wrapped: descriptors from 2^30 launches ago would look current
+    CUDA_TRY(c, cudaMemsetAsync((char*)c->scratch + sizeof(ScratchHeader), 0, c->scratch_tiles * sizeof(unsigned long long), stream));
+    c->epoch = 1;
+  }
+  Params p;
+  p.rows = in->rows;
+  p.row_ptr = in->row_ptr;
+  p.rows_bytes = in->rows_bytes;
+  p.n_nodes = in->n_nodes;
+  p.node_base = in->node_base;
+  p.num_tiles = tiles;
+  p.epoch = c->epoch;
+  p.max_digits = c->max_digits;
+  p.flags = out->flags;
+  p.gpu_idx = out->gpu_idx;
+  p.gpu_total = out->gpu_total;
+  p.gpu_vals = out->gpu_vals;
+  p.defer = out->defer;
+  p.counts = out->counts;
+  p.out_cap = out->out_cap;
+  p.defer_cap = out->defer ? out->defer_cap : 0;
+  p.scratch = (ScratchHeader*)c->scratch;
+  p.tile_state = (unsigned long long*)((char*)c->scratch + sizeof(ScratchHeader));
+  const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(c->sm_count * c->ctas_per_sm[v]));
+  var.launch(p, grid, var.smem, stream);
+  CUDA_TRY(c, cudaGetLastError());
+  c->launches++;
+  return GNC_OK;
+}
+
+uint64_t gnc_launch_count(const gnc_ctx* c) { return c ? c->launches : 0; }
+
+int gnc_unicode_tables(const uint32_t** nd_runs, int* n_runs, const uint32_t** spaces, int* n_spaces) {
+  static const uint32_t runs[GNC_ND_RUNS] = {GNC_ND_RUN_LIST};
+  static const uint32_t ws[GNC_WIDE_SPACES] = {GNC_WIDE_SPACE_LIST};
+  if (nd_runs) *nd_runs = runs;
+  if (n_runs) *n_runs = GNC_ND_RUNS;
+  if (spaces) *spaces = ws;
+  if (n_spaces) *n_spaces = GNC_WIDE_SPACES;
+  return GNC_OK;
+}
+
+const char* gnc_last_error(const gnc_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+}  // extern "C"
+
+// =================================================================================================
+// Host-buffer path: the shard lives in host memory; results come back to host memory.
+// =================================================================================================
+namespace {
+
+template <class T>
+int regrow(gnc_ctx* c, T** p, size_t count) {
+  if (*p) CUDA_TRY(c, cudaFree(*p));
+  *p = nullptr;
+  CUDA_TRY(c, cudaMalloc((void**)p, count * sizeof(T)));
+  return GNC_OK;
+}
+
+int ensure_host_stage(gnc_ctx* c, gnc_ctx::HostStage& h, size_t rows_bytes, size_t nodes, size_t defer_cap) {
+  if (!h.stream) {
+    CUDA_TRY(c, cudaStreamCreateWithFlags(&h.stream, cudaStreamNonBlocking));
+    CUDA_TRY(c, cudaEventCreateWithFlags(&h.done, cudaEventDisableTiming));
+    CUDA_TRY(c, cudaEventCreateWithFlags(&h.kernel, cudaEventDisableTiming));
+    CUDA_TRY(c, cudaMalloc((void**)&h.d_counts, GNC_N_COUNTS * sizeof(int64_t)));
+    CUDA_TRY(c, cudaMallocHost((void**)&h.h_counts, GNC_N_COUNTS * sizeof(int64_t)));
+  }
+  int rc;
+  if (rows_bytes + 64 > h.rows_cap) {
+    size_t cap = rows_bytes + rows_bytes / 8 + 4096;
+    if ((rc = regrow(c, &h.d_rows, cap))) return rc;
+    h.rows_cap = cap;
+  }
+  if (nodes > h.nodes_cap) {
+    size_t cap = nodes + nodes / 8 + 1024;
+    if ((rc = regrow(c, &h.d_row_ptr, cap + 8))) return rc;
+    if ((rc = regrow(c, &h.d_flags, cap))) return rc;
+    if ((rc = regrow(c, &h.d_idx, cap))) return rc;
+    if ((rc = regrow(c, &h.d_total, cap))) return rc;
+    if ((rc = regrow(c, &h.d_vals, cap * 4))) return rc;
+    h.nodes_cap = cap;
+  }
+  if (defer_cap > h.defer_cap) {
+    if ((rc = regrow(c, &h.d_defer, defer_cap))) return rc;
+    h.defer_cap = defer_cap;
+  }
+  return GNC_OK;
+}
+
+}  // namespace
+
+extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_result* out) {
+  if (!c) return GNC_ERR_ARG;
+  if (!in || !out || !out->counts) return fail(c, GNC_ERR_ARG, "null batch, result or counts");
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  memset(out->counts, 0, GNC_N_COUNTS * sizeof(int64_t));
+  if (in->n_nodes == 0) return GNC_OK;
+  if (!in->rows || !in->row_ptr || !out->flags || !out->gpu_idx || !out->gpu_total || !out->gpu_vals)
+    return fail(c, GNC_ERR_ARG, "null host buffer");
+  // Chunks of ~1M nodes: chunk k+1's upload overlaps chunk k's kernel and download.
+  const uint32_t kChunk = 1u << 20;
+  const uint32_t n = in->n_nodes;
+  uint64_t g_total = 0, d_total = 0;
+  int64_t acc[GNC_N_COUNTS] = {0};
+  unsigned __int128 key[4] = {0, 0, 0, 0};
+  struct Pending {
+    bool live = false;
+    uint32_t first = 0, cnt = 0;
+    uint64_t g_at = 0, d_at = 0;
+  } pend[2];
+  auto drain = [&](int b) -> int {
+    gnc_ctx::HostStage& h = c->hs[b];
+    Pending& q = pend[b];
+    if (!q.live) return GNC_OK;
+    CUDA_TRY(c, cudaEventSynchronize(h.done));
+    const uint64_t g = (uint64_t)h.h_counts[GNC_C_GPU_NODES];
+    const uint64_t d = std::min<uint64_t>((uint64_t)h.h_counts[GNC_C_DEFERRED], h.defer_cap);
+    const uint64_t room = out->out_cap > g_total ? out->out_cap - g_total : 0, gk = std::min(g, room);
+    CUDA_TRY(c, cudaMemcpyAsync(out->flags + q.first, h.d_flags, q.cnt, cudaMemcpyDeviceToHost, h.stream));
+    if (gk) {
+      CUDA_TRY(c, cudaMemcpyAsync(out->gpu_idx + g_total, h.d_idx, gk * 4, cudaMemcpyDeviceToHost, h.stream));
+      CUDA_TRY(c, cudaMemcpyAsync(out->gpu_total + g_total, h.d_total, gk * 8, cudaMemcpyDeviceToHost, h.stream));
+      CUDA_TRY(c, cudaMemcpyAsync(out->gpu_vals + 4 * g_total, h.d_vals, gk * 32, cudaMemcpyDeviceToHost, h.stream));
+    }
+    const uint64_t droom = out->defer && out->defer_cap > d_total ? out->defer_cap - d_total : 0, dk = std::min(d, droom);
+    if (dk)
+      CUDA_TRY(c, cudaMemcpyAsync(out->defer + d_total, h.d_defer, dk * sizeof(gnc_defer_rec), cudaMemcpyDeviceToHost, h.stream));
+    CUDA_TRY(c, cudaStreamSynchronize(h.stream));
+    for (int s : {GNC_C_GPU_NODES, GNC_C_READY_NODES, GNC_C_DEFERRED, GNC_C_SCANNED, GNC_C_MALFORMED})
+      acc[s] += h.h_counts[s];
+    acc[GNC_C_OUT_DROPPED] += h.h_counts[GNC_C_OUT_DROPPED] + (int64_t)(g - gk);
+    acc[GNC_C_DEFER_DROPPED] += h.h_counts[GNC_C_DEFER_DROPPED] + (int64_t)((uint64_t)h.h_counts[GNC_C_DEFERRED] - dk);
+    for (int k = 0; k < 4; k++)
+      key[k] += ((unsigned __int128)(uint64_t)h.h_counts[GNC_C_KEY_HI + k] << 64) | (uint64_t)h.h_counts[GNC_C_KEY_LO + k];
+    g_total += gk;
+    d_total += dk;
+    q.live = false;
+    return GNC_OK;
+  };
+  int b = 0;
+  const uint32_t defer_cap = out->defer ? std::max<uint32_t>(out->defer_cap, 1) : 1;
+  for (uint32_t first = 0; first < n; first += kChunk, b ^= 1) {
+    int rc = drain(b);
+    if (rc) return rc;
+    const uint32_t cnt = std::min(kChunk, n - first);
+    const uint64_t b0 = in->row_ptr[first], b1 = in->row_ptr[first + cnt];
+    if (b1 < b0 || b1 > in->rows_bytes) return fail(c, GNC_ERR_ARG, "row_ptr is not monotone inside rows_bytes");
+    gnc_ctx::HostStage& h = c->hs[b];
+    if ((rc = ensure_host_stage(c, h, b1 - b0 + 16, cnt, defer_cap))) return rc;
+    // rows are copied from a 16-byte aligned source offset so row_ptr can stay absolute minus a constant
+    const uint64_t a0 = b0 & ~15ull;
+    CUDA_TRY(c, cudaMemcpyAsync(h.d_rows, in->rows + a0, b1 - a0, cudaMemcpyHostToDevice, h.stream));
+    CUDA_TRY(c, cudaMemsetAsync(h.d_rows + (b1 - a0), 0, 48, h.stream));
+    CUDA_TRY(c, cudaMemcpyAsync(h.d_row_ptr, in->row_ptr + first, (cnt + 1) * 4ull, cudaMemcpyHostToDevice, h.stream));
+    gnc_batch db;
+    db.rows = h.d_rows - a0;  // device offsets == host offsets (never dereferenced below a0), so are defer offsets
+    db.row_ptr = h.d_row_ptr;
+    db.rows_bytes = b1;
+    db.n_nodes = cnt;
+    db.node_base = in->node_base + first;
+    gnc_result dr;
+    dr.flags = h.d_flags;
+    dr.gpu_idx = h.d_idx;
+    dr.gpu_total = h.d_total;
+    dr.gpu_vals = h.d_vals;
+    dr.defer = h.d_defer;
+    dr.counts = h.d_counts;
+    dr.out_cap = cnt;
+    dr.defer_cap = (uint32_t)h.defer_cap;
+    // the tail of row_ptr the bulk copy may touch
+    CUDA_TRY(c, cudaMemsetAsync(h.d_row_ptr + cnt + 1, 0xFF, 7 * 4, h.stream));
+    // both stages' kernels share the context's scratch: this one starts after the other stage's has ended
+    if (c->hs[b ^ 1].kernel && pend[b ^ 1].live) CUDA_TRY(c, cudaStreamWaitEvent(h.stream, c->hs[b ^ 1].kernel, 0));
+    if ((rc = gnc_classify(c, &db, &dr, h.stream))) return rc;
+    CUDA_TRY(c, cudaEventRecord(h.kernel, h.stream));
+    CUDA_TRY(c, cudaMemcpyAsync(h.h_counts, h.d_counts, GNC_N_COUNTS * sizeof(int64_t), cudaMemcpyDeviceToHost, h.stream));
+    CUDA_TRY(c, cudaEventRecord(h.done, h.stream));
+    pend[b].live = true;
+    pend[b].first = first;
+    pend[b].cnt = cnt;
+  }
+  for (int k = 0; k < 2; k++, b ^= 1) {
+    int rc = drain(b);
+    if (rc) return rc;
+  }
+  memcpy(out->counts, acc, sizeof(acc));
+  for (int k = 0; k < 4; k++) {
+    out->counts[GNC_C_KEY_LO + k] = (int64_t)(uint64_t)key[k];
+    out->counts[GNC_C_KEY_HI + k] = (int64_t)(uint64_t)(key[k] >> 64);
+  }
+  if (acc[GNC_C_OUT_DROPPED] || acc[GNC_C_DEFER_DROPPED])
+    return fail(c, GNC_ERR_OVERFLOW, "out_cap or defer_cap too small; see counts[13], counts[14]");
+  return GNC_OK;
+}
+
+extern "C" void gnc_destroy(gnc_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  comm_destroy(c);
+  for (auto& h : c->hs) {
+    if (h.stream) cudaStreamDestroy(h.stream);
+    if (h.done) cudaEventDestroy(h.done);
+    if (h.kernel) cudaEventDestroy(h.kernel);
+    cudaFree(h.d_rows);
+    cudaFree(h.d_row_ptr);
+    cudaFree(h.d_flags);
+    cudaFree(h.d_idx);
+    cudaFree(h.d_total);
+    cudaFree(h.d_vals);
+    cudaFree(h.d_defer);
+    cudaFree(h.d_counts);
+    if (h.h_counts) cudaFreeHost(h.h_counts);
+  }
+  cudaFree(c->scratch);
+  delete c;
+}
+
+
+// =================================================================================================
+// Multi-GPU: NCCL, resolved at run time so the library loads (and the CPU tests run) without it and
+// so a process that already holds a libnccl.so.2 (torch's) shares that one copy.
+// =================================================================================================
+namespace {
+
+struct NcclId {
+  char bytes[128];
+};
+struct NcclApi {
+  int (*GetUniqueId)(NcclId*) = nullptr;
+  int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  void* lib = nullptr;
+  std::string err;
+};
+constexpr int kNcclUint32 = 3, kNcclInt64 = 4;
+
+NcclApi* nccl_api() {
+  static NcclApi api;
+  if (api.lib || !api.err.empty()) return &api;
+  const char* names[] = {getenv("GNC_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    if (!n) continue;
+    api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (api.lib) break;
+  }
+  if (!api.lib) {
+    api.err = std::string("cannot load libnccl: ") + dlerror();
+    return &api;
+  }
+#define GNC_SYM(field, name)                                        \
+  *(void**)(&api.field) = dlsym(api.lib, name);                      \
+  if (!api.field) api.err = std::string("libnccl lacks ") + name;
+  GNC_SYM(GetUniqueId, "ncclGetUniqueId")
+  GNC_SYM(CommInitRank, "ncclCommInitRank")
+  GNC_SYM(CommDestroy, "ncclCommDestroy")
+  GNC_SYM(AllGather, "ncclAllGather")
+  GNC_SYM(Broadcast, "ncclBroadcast")
+  GNC_SYM(GroupStart, "ncclGroupStart")
+  GNC_SYM(GroupEnd, "ncclGroupEnd")
+  GNC_SYM(GetErrorString, "ncclGetErrorString")
+#undef GNC_SYM
+  return &api;
+}
+
+#define NCCL_TRY(c, expr)                                                                                 \
+  do {                                                                                                    \
+    int r_ = (expr);                                                                                      \
+    if (r_ != 0) return fail(c, GNC_ERR_COMM, std::string(#expr) + ": " + nccl_api()->GetErrorString(r_)); \
+  } while (0)
+
+int comm_init(gnc_ctx* c, const void* id, size_t id_len) {
+  NcclApi* n = nccl_api();
+  if (!n->err.empty()) return fail(c, GNC_ERR_COMM, n->err);
+  if (!id || id_len != sizeof(NcclId)) return fail(c, GNC_ERR_ARG, "world > 1 needs the 128-byte id from gnc_comm_id");
+  NcclId nid;
+  memcpy(nid.bytes, id, sizeof(nid));
+  NCCL_TRY(c, n->CommInitRank(&c->comm, c->world, nid, c->rank));
+  CUDA_TRY(c, cudaMalloc((void**)&c->d_all_counts, (size_t)c->world * GNC_N_COUNTS * sizeof(int64_t)));
+  CUDA_TRY(c, cudaMallocHost((void**)&c->h_all_counts, (size_t)c->world * GNC_N_COUNTS * sizeof(int64_t)));
+  return GNC_OK;
+}
+
+void comm_destroy(gnc_ctx* c) {
+  if (c->comm) nccl_api()->CommDestroy(c->comm);
+  c->comm = nullptr;
+  cudaFree(c->d_all_counts);
+  if (c->h_all_counts) cudaFreeHost(c->h_all_counts);
+}
+
+}  // namespace
+
+extern "C" int gnc_comm_id(void* id, size_t cap, size_t* len) {
+  NcclApi* n = nccl_api();
+  if (!n->err.empty() || !id || cap < sizeof(NcclId)) return n->err.empty() ? GNC_ERR_ARG : GNC_ERR_COMM;
+  NcclId nid;
+  if (n->GetUniqueId(&nid) != 0) return GNC_ERR_COMM;
+  memcpy(id, nid.bytes, sizeof(nid));
+  if (len) *len = sizeof(nid);
+  return GNC_OK;
+}
+
+extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result* all, void* cuda_stream) {
+  if (!c) return GNC_ERR_ARG;
+  if (!local || !all || !local->counts || !all->counts) return fail(c, GNC_ERR_ARG, "null result or counts");
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  if (c->world == 1) {  // nothing to combine: `all` may alias `local`
+    if (all->counts != local->counts)
+      CUDA_TRY(c, cudaMemcpyAsync(all->counts, local->counts, GNC_N_COUNTS * sizeof(int64_t), cudaMemcpyDeviceToDevice, stream));
+    return GNC_OK;
+  }
+  if (!c->comm) return fail(c, GNC_ERR_STATE, "context has no communicator");
+  NcclApi* n = nccl_api();
+  // 1. every rank's counts block to every rank; the sum (exact, 128-bit for the key totals) is the
+  //    all-reduce of the counts, and the per-rank GPU-node counts give the gather offsets
+  NCCL_TRY(c, n->AllGather(local->counts, c->d_all_counts, GNC_N_COUNTS, kNcclInt64, c->comm, stream));
+  CUDA_TRY(c, cudaMemcpyAsync(c->h_all_counts, c->d_all_counts, (size_t)c->world * GNC_N_COUNTS * sizeof(int64_t),
+                              cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(c, cudaStreamSynchronize(stream));
+  int64_t sum[GNC_N_COUNTS] = {0};
+  unsigned __int128 key[4] = {0, 0, 0, 0};
+  std::vector<uint64_t> off(c->world + 1, 0);
+  for (int r = 0; r < c->world; r++) {
+    const int64_t* cr = c->h_all_counts + (size_t)r * GNC_N_COUNTS;
+    for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] += cr[s];
+    for (int k = 0; k < 4; k++)
+      key[k] += ((unsigned __int128)(uint64_t)cr[GNC_C_KEY_HI + k] << 64) | (uint64_t)cr[GNC_C_KEY_LO + k];
+    off[r + 1] = off[r] + (uint64_t)cr[GNC_C_GPU_NODES];
+  }
+  for (int k = 0; k < 4; k++) {
+    sum[GNC_C_KEY_LO + k] = (int64_t)(uint64_t)key[k];
+    sum[GNC_C_KEY_HI + k] = (int64_t)(uint64_t)(key[k] >> 64);
+  }
+  if (off[c->world] > all->out_cap) return fail(c, GNC_ERR_OVERFLOW, "all.out_cap is smaller than the fleet's GPU-node count");
+  memcpy(c->h_all_counts, sum, sizeof(sum));  // reuse the pinned block as the upload source
+  CUDA_TRY(c, cudaMemcpyAsync(all->counts, c->h_all_counts, sizeof(sum), cudaMemcpyHostToDevice, stream));
+  // 2. all-gather-v of the compacted records: one broadcast per rank into its rank-ordered slice
+  NCCL_TRY(c, n->GroupStart());
+  for (int r = 0; r < c->world; r++) {
+    const uint64_t cnt = off[r + 1] - off[r];
+    if (!cnt) continue;
+    NCCL_TRY(c, n->Broadcast(local->gpu_idx, all->gpu_idx + off[r], cnt, kNcclUint32, r, c->comm, stream));
+    if (all->gpu_total && local->gpu_total)
+      NCCL_TRY(c, n->Broadcast(local->gpu_total, all->gpu_total + off[r], cnt, kNcclInt64, r, c->comm, stream));
+    if (all->gpu_vals && local->gpu_vals)
+      NCCL_TRY(c, n->Broadcast(local->gpu_vals, all->gpu_vals + 4 * off[r], 4 * cnt, kNcclInt64, r, c->comm, stream));
+  }
+  NCCL_TRY(c, n->GroupEnd());
+  c->launches += 2;
+  return GNC_OK;
+}

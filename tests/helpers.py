@@ -56,10 +56,13 @@ def expected_outputs(truth: Dict[str, np.ndarray], tid: np.ndarray, node_base: i
     counts[2] = int(((flags & F_DEFERRED) != 0).sum())
     counts[3] = len(tid)
     for k in range(4):
-        t = int(sum(int(x) for x in vals[:, k])) if len(sel) < 200000 else int(vals[:, k].astype(object).sum())
-        counts[4 + k] = np.int64(np.uint64(t & ((1 << 64) - 1)).astype(np.int64)) if t >= 0 else np.int64(
-            np.uint64((t + (1 << 128)) & ((1 << 64) - 1)).astype(np.int64))
-        counts[8 + k] = (t >> 64)
+        col = vals[:, k]
+        if len(col) == 0 or int(np.abs(col).max()) < (1 << 36):
+            t = int(col.sum())
+        else:
+            t = int(col.astype(object).sum())
+        counts[4 + k] = np.array([t & ((1 << 64) - 1)], dtype=np.uint64).view(np.int64)[0]
+        counts[8 + k] = t >> 64
     return {"flags": flags, "gpu_idx": (sel + node_base).astype(np.uint32), "gpu_total": truth["total"][tid[sel]],
             "gpu_vals": vals, "counts": counts, "deferred_nodes": (np.nonzero(flags & F_DEFERRED)[0] + node_base)}
 

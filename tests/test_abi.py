@@ -1,0 +1,51 @@
+"""CPU-side checks of the C ABI: the library loads, exports what include/gnc.h declares, and the
+Unicode tables compiled into it are this interpreter's."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from k8s_gpu_node_checker_b200 import native
+from oracle import cgn_oracle as o
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(native.LIB_PATH):
+        native.build()
+    return native.lib()
+
+
+def test_header_and_library_agree(lib):
+    hdr = open(os.path.join(ROOT, "include", "gnc.h")).read()
+    declared = set(re.findall(r"\b(gnc_[a-z_]+)\s*\(", hdr))
+    assert declared == set(native.EXPORTS)
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert int(re.search(r"#define GNC_ABI_VERSION (\d+)", hdr).group(1)) == lib.gnc_abi_version() == native.ABI_VERSION
+
+
+def test_struct_layouts_match_header():
+    assert ctypes.sizeof(native.Batch) == 32
+    assert ctypes.sizeof(native.DeferRec) == 36
+    assert ctypes.sizeof(native.Result) == 56
+
+
+def test_unicode_tables_are_this_interpreters(lib):
+    runs, spaces = native.unicode_tables()
+    assert runs == o.unicode_decimal_runs()
+    assert spaces == o.unicode_wide_spaces()
+
+
+def test_no_cpu_fallback_in_product():
+    """The product package never imports the oracle."""
+    pkg = os.path.join(ROOT, "k8s-gpu-node-checker_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", txt, re.M), f
+                assert "pnl_oracle" not in txt, f
