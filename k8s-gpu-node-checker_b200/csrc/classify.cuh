@@ -1,9 +1,12 @@
 // classify.cuh -- the node-classification kernel (sm_100a).
 //
-// One persistent CTA per tile stream.  A producer warp takes tile tickets in fleet order and stages
-// each tile's bytes in shared memory with TMA bulk copies (cp.async.bulk + mbarrier); TN "capacity"
-// threads and TN "condition" threads each walk one node's row out of shared memory; GPU nodes are
-// compacted in fleet order with warp ballots, a CTA scan and a decoupled look-back across tiles.
+// Persistent CTAs, four warp roles.  A producer warp takes tile tickets in fleet order and stages each
+// tile's bytes in shared memory with TMA bulk copies (cp.async.bulk + mbarrier).  TN "capacity"
+// threads and TN "condition" threads each walk one node's row out of shared memory.  GPU nodes are
+// compacted in fleet order: warp ballots give ranks, two scan warps turn per-warp counts into output
+// positions with a 512-tile-wide decoupled look-back over global descriptors, and the capacity
+// threads write a tile's records one iteration later (from a thread-private stash), so no walker
+// ever waits for a global-memory round trip.
 //
 // Reference behaviour implemented (file:line in /root/reference/check-gpu-node.py):
 //   key match + quantity parse  :186-195      Ready test  :172-178      gpus sum / filter  :201, :222-225
@@ -16,6 +19,17 @@
 #include "unicode_tables.inc"
 
 namespace gnc {
+
+#ifdef GNC_TRACE
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define GNC_T(slot, it_, val) do { if (p.trace && (it_) < 64) p.trace[((size_t)blockIdx.x * 64 + (it_)) * 8 + (slot)] = (val); } while (0)
+#else
+#define GNC_T(slot, it_, val) do { } while (0)
+#endif
 
 // ------------------------------------------------------------------------------------------------
 // Library-owned scratch (global memory beyond the caller's inputs and outputs).
@@ -30,10 +44,13 @@ struct ScratchHeader {
 };
 static_assert(sizeof(ScratchHeader) == 256, "tile states start 256 bytes in");
 
-// Tile descriptor for the look-back: [63:62] status, [61:32] launch epoch, [31:0] GPU-node count.
-constexpr uint64_t kStatusAggregate = 1ull << 62;
-constexpr uint64_t kStatusInclusive = 2ull << 62;
-constexpr uint32_t kEpochMask = (1u << 30) - 1;
+// Look-back descriptors, one pair per tile, valid only when their tag equals the launch's epoch
+// (1 .. 2^22-1; zeroed memory is never valid):
+//   agg[t] u32: [31:10] epoch, [9:0]  GPU nodes in tile t
+//   inc[t] u64: [63:32] epoch, [31:0] GPU nodes in tiles 0..t
+constexpr uint32_t kEpochMask = (1u << 22) - 1;
+constexpr int kLookbackSpan = 16;                   // tiles per lane per round
+constexpr int kLookbackWindow = 32 * kLookbackSpan; // tiles per round
 
 struct Params {
   const uint8_t* rows;
@@ -53,7 +70,9 @@ struct Params {
   uint32_t out_cap;
   uint32_t defer_cap;
   ScratchHeader* scratch;
-  unsigned long long* tile_state;
+  unsigned long long* inc;  // [tiles rounded up to the look-back window]
+  uint32_t* agg;            // likewise
+  unsigned long long* trace;  // debug builds only (GNC_TRACE): [cta][iteration][8] timestamps
 };
 
 __constant__ uint32_t c_nd_runs[GNC_ND_RUNS] = {GNC_ND_RUN_LIST};
@@ -89,6 +108,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
   } while (!ok);
 }
+// same, for waits expected to last microseconds: sleep between polls so the issue slots go to walkers
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  uint32_t addr = smem_addr(bar), ok;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (ok) break;
+    __nanosleep(64);
+  }
+}
 // global -> shared bulk copy; src, dst and bytes are multiples of 16.
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -106,6 +140,14 @@ __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned lon
 }
 __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
   asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint32_t* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -263,108 +305,213 @@ __device__ __forceinline__ bool row_sections(const uint8_t* buf, uint32_t s, uin
   return true;
 }
 
-struct CapResult {
-  long long v[4];
-  uint32_t present;  // bit k: key k kept
-  uint32_t big;      // bit k: key k kept but wider than 18 digits
-  bool malformed;
+// ------------------------------------------------------------------------------------------------
+// Per-node result of a walk.  Values travel as four int16 (a quantity is almost always one digit);
+// a node with a value outside int16 is "wide": its exact values are read again, out of line, where
+// they are needed.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t R_PRESENT = 0xFu;         // bits 0..3: key k kept in gpu_breakdown
+constexpr uint32_t R_BIG_SHIFT = 4;          // bits 4..7: key k kept but wider than 18 digits
+constexpr uint32_t R_WIDE = 1u << 8;
+constexpr uint32_t R_MALFORMED = 1u << 9;
+constexpr uint32_t R_READY = 1u << 10;
+
+struct NodeResult {
+  uint32_t v01, v23;  // int16 x 4
+  uint32_t bits;
 };
 
-__device__ __forceinline__ void walk_capacity(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, CapResult& r) {
-  r.v[0] = r.v[1] = r.v[2] = r.v[3] = 0;
-  r.present = r.big = 0;
-  uint32_t pos, cap_e;
-  r.malformed = !row_sections(buf, s, e, &pos, &cap_e);
-  if (r.malformed) return;
+__device__ __forceinline__ void set_value(NodeResult& r, int k, int st, long long val) {
+  const uint32_t bit = 1u << k;
+  r.bits = (r.bits & ~(bit | (bit << R_BIG_SHIFT))) | (st != Q_ABSENT ? bit : 0u) | (st == Q_BIG ? bit << R_BIG_SHIFT : 0u);
+  if (st != Q_OK) val = 0;
+  if ((unsigned long long)(val + 32768) >= 65536ull) {
+    r.bits |= R_WIDE;
+    val = 0;
+  }
+  const uint32_t sh = (k & 1) << 4, m = 0xFFFFu << sh, x = ((uint32_t)val & 0xFFFFu) << sh;
+  if (k & 2) r.v23 = (r.v23 & ~m) | x;
+  else r.v01 = (r.v01 & ~m) | x;
+}
+
+// Slow, general, out-of-line walk of one row from a generic pointer: every escape, exact 64-bit
+// values, value-text positions.  Rows with 32-bit length escapes, rows of tiles too large to stage,
+// wide and deferred nodes come here; the hot path below never does.
+struct SlowRow {
+  long long v[4];
+  uint32_t off[4], len[4];
+  uint32_t bits;  // R_PRESENT / big / R_MALFORMED / R_READY (never R_WIDE)
+};
+
+__device__ __noinline__ void slow_row(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, SlowRow* out) {
+  for (int k = 0; k < 4; k++) {
+    out->v[k] = 0;
+    out->off[k] = 0xFFFFFFFFu;
+    out->len[k] = 0;
+  }
+  uint32_t bits = 0, pos, cap_e;
+  if (!row_sections(buf, s, e, &pos, &cap_e)) {
+    out->bits = R_MALFORMED;
+    return;
+  }
   while (pos < cap_e) {
     Entry en = read_entry(buf, pos, cap_e);
     if (!en.ok) {
-      r.malformed = true;
+      bits |= R_MALFORMED;
       break;
     }
     int k = -1;
-    if (en.kl == 14) {
-      if (en.k01 == pack4("nv", 0, 2) && key_tail_eq<14>(buf, en.kp, "nvidia.com/gpu")) k = 0;
-    } else if (en.kl == 11) {
-      if (en.k01 == pack4("am", 0, 2) && key_tail_eq<11>(buf, en.kp, "amd.com/gpu")) k = 1;
-    } else if (en.kl == 18) {
-      if (en.k01 == pack4("gp", 0, 2) && key_tail_eq<18>(buf, en.kp, "gpu.intel.com/i915")) k = 2;
-    } else if (en.kl == 13) {
-      if (en.k01 == pack4("in", 0, 2) && key_tail_eq<13>(buf, en.kp, "intel.com/gpu")) k = 3;
-    }
-    uint32_t vp = en.kp + en.kl;
+    if (en.kl == 14 && en.k01 == pack4("nv", 0, 2) && key_tail_eq<14>(buf, en.kp, "nvidia.com/gpu")) k = 0;
+    if (en.kl == 11 && en.k01 == pack4("am", 0, 2) && key_tail_eq<11>(buf, en.kp, "amd.com/gpu")) k = 1;
+    if (en.kl == 18 && en.k01 == pack4("gp", 0, 2) && key_tail_eq<18>(buf, en.kp, "gpu.intel.com/i915")) k = 2;
+    if (en.kl == 13 && en.k01 == pack4("in", 0, 2) && key_tail_eq<13>(buf, en.kp, "intel.com/gpu")) k = 3;
+    const uint32_t vp = en.kp + en.kl;
     if (k >= 0) {  // a repeated key overwrites: dict / json.loads last-wins
-      int st = Q_ABSENT;
       long long val = 0;
-      if (en.vl == 1) {
-        uint32_t d = (uint32_t)buf[vp] - '0';
-        if (d <= 9u) {
-          st = Q_OK;
-          val = d;
-        } else {
-          st = parse_quantity_general(buf + vp, 1, max_digits, &val);
-        }
-      } else if (en.vl != 0) {
-        st = parse_quantity_general(buf + vp, en.vl, max_digits, &val);
-      }
-      uint32_t bit = 1u << k;
-      r.present = (r.present & ~bit) | (st != Q_ABSENT ? bit : 0u);
-      r.big = (r.big & ~bit) | (st == Q_BIG ? bit : 0u);
-      val = (st == Q_OK) ? val : 0;
-      if (k == 0) r.v[0] = val;
-      else if (k == 1) r.v[1] = val;
-      else if (k == 2) r.v[2] = val;
-      else r.v[3] = val;
+      const int st = en.vl ? parse_quantity_general(buf + vp, en.vl, max_digits, &val) : Q_ABSENT;
+      const uint32_t bit = 1u << k;
+      bits = (bits & ~(bit | (bit << R_BIG_SHIFT))) | (st != Q_ABSENT ? bit : 0u) | (st == Q_BIG ? bit << R_BIG_SHIFT : 0u);
+      out->v[k] = st == Q_OK ? val : 0;
+      out->off[k] = st == Q_ABSENT ? 0xFFFFFFFFu : vp;
+      out->len[k] = st == Q_ABSENT ? 0u : en.vl;
     }
     pos = vp + en.vl;
   }
-}
-
-// bit 0: Ready, bit 1: malformed
-__device__ __forceinline__ uint32_t walk_conditions(const uint8_t* buf, uint32_t s, uint32_t e) {
-  uint32_t cap_b, pos;
-  if (!row_sections(buf, s, e, &cap_b, &pos)) return 2u;
+  pos = cap_e;
   while (pos < e) {
     Entry en = read_entry(buf, pos, e);
-    if (!en.ok) return 2u;
+    if (!en.ok) {
+      bits |= R_MALFORMED;
+      break;
+    }
     if (en.kl == 5 && en.vl == 4 && en.k01 == pack4("Re", 0, 2) && ld32u(buf, en.kp + 2) == pack4("adyT", 0, 4) &&
-        (ld32u(buf, en.kp + 6) & 0xFFFFFFu) == pack4("rue", 0, 3))
-      return 1u;  // first hit returns (check-gpu-node.py:176-177)
+        (ld32u(buf, en.kp + 6) & 0xFFFFFFu) == pack4("rue", 0, 3)) {
+      bits |= R_READY;  // first hit returns (check-gpu-node.py:176-177)
+      break;
+    }
     pos = en.kp + en.kl + en.vl;
   }
-  return 0u;
+  out->bits = bits;
 }
 
-// Deferred node: walk its row again (from global memory) and record where each kept value's text is.
+__device__ __noinline__ void slow_row_packed(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, NodeResult* r) {
+  SlowRow sr;
+  slow_row(buf, s, e, max_digits, &sr);
+  r->v01 = r->v23 = 0;
+  r->bits = sr.bits;
+  for (int k = 0; k < 4; k++) {
+    const bool fits = (unsigned long long)(sr.v[k] + 32768) < 65536ull;
+    if (!fits) r->bits |= R_WIDE;
+    const uint32_t x = fits ? ((uint32_t)sr.v[k] & 0xFFFFu) : 0u;
+    if (k & 2) r->v23 |= x << ((k & 1) << 4);
+    else r->v01 |= x << ((k & 1) << 4);
+  }
+}
+
 __device__ __noinline__ void emit_defer(const Params& p, uint32_t node, uint32_t s, uint32_t e, uint32_t slot) {
+  SlowRow sr;
+  slow_row(p.rows, s, e, p.max_digits, &sr);
   gnc_defer_rec rec;
   rec.node = p.node_base + node;
   for (int k = 0; k < 4; k++) {
-    rec.off[k] = 0xFFFFFFFFu;
-    rec.len[k] = 0;
-  }
-  const uint8_t* buf = p.rows;
-  uint32_t pos, cap_e;
-  if (row_sections(buf, s, e, &pos, &cap_e)) {
-    while (pos < cap_e) {
-      Entry en = read_entry(buf, pos, cap_e);
-      if (!en.ok) break;
-      int k = -1;
-      if (en.kl == 14 && en.k01 == pack4("nv", 0, 2) && key_tail_eq<14>(buf, en.kp, "nvidia.com/gpu")) k = 0;
-      if (en.kl == 11 && en.k01 == pack4("am", 0, 2) && key_tail_eq<11>(buf, en.kp, "amd.com/gpu")) k = 1;
-      if (en.kl == 18 && en.k01 == pack4("gp", 0, 2) && key_tail_eq<18>(buf, en.kp, "gpu.intel.com/i915")) k = 2;
-      if (en.kl == 13 && en.k01 == pack4("in", 0, 2) && key_tail_eq<13>(buf, en.kp, "intel.com/gpu")) k = 3;
-      uint32_t vp = en.kp + en.kl;
-      if (k >= 0) {
-        long long val;
-        int st = en.vl ? parse_quantity_general(buf + vp, en.vl, p.max_digits, &val) : Q_ABSENT;
-        rec.off[k] = st == Q_ABSENT ? 0xFFFFFFFFu : vp;
-        rec.len[k] = st == Q_ABSENT ? 0u : en.vl;
-      }
-      pos = vp + en.vl;
-    }
+    rec.off[k] = sr.off[k];
+    rec.len[k] = sr.len[k];
   }
   p.defer[slot] = rec;
+}
+
+// A key candidate (length and first two bytes fit one of the four keys): compare the rest of the key
+// with per-key constants picked by select (no divergence between lanes holding different keys) and
+// parse the value.  One call per node in the common case, with the warp converged.
+__device__ __forceinline__ void resolve_candidate(const uint8_t* buf, uint32_t cand, uint32_t kp, int max_digits, NodeResult& r) {
+  const int k = (cand >> 1) & 3;
+  const uint32_t vl = cand >> 3;
+  // key bytes [2, 18): words at +2, +6, +10, +14
+  const uint32_t e0 = k == 0 ? pack4("idia", 0, 4) : k == 1 ? pack4("d.co", 0, 4) : k == 2 ? pack4("u.in", 0, 4) : pack4("tel.", 0, 4);
+  const uint32_t e1 = k == 0 ? pack4(".com", 0, 4) : k == 1 ? pack4("m/gp", 0, 4) : k == 2 ? pack4("tel.", 0, 4) : pack4("com/", 0, 4);
+  const uint32_t e2 = k == 0 ? pack4("/gpu", 0, 4) : k == 1 ? pack4("u", 0, 1) : k == 2 ? pack4("com/", 0, 4) : pack4("gpu", 0, 3);
+  const uint32_t m2 = k == 1 ? 0xFFu : k == 3 ? 0xFFFFFFu : 0xFFFFFFFFu;
+  const uint32_t e3 = k == 2 ? pack4("i915", 0, 4) : 0u;
+  const uint32_t m3 = k == 2 ? 0xFFFFFFFFu : 0u;
+  const bool eq = ld32u(buf, kp + 2) == e0 && ld32u(buf, kp + 6) == e1 && (ld32u(buf, kp + 10) & m2) == e2 &&
+                  (ld32u(buf, kp + 14) & m3) == e3;
+  if (!eq) return;
+  const uint32_t kl = k == 0 ? 14u : k == 1 ? 11u : k == 2 ? 18u : 13u;
+  const uint32_t vp = kp + kl;
+  int st = Q_ABSENT;
+  long long val = 0;
+  if (vl == 1) {
+    const uint32_t d = (uint32_t)buf[vp] - '0';
+    if (d <= 9u) {
+      st = Q_OK;
+      val = d;
+    } else {
+      st = parse_quantity_general(buf + vp, 1, max_digits, &val);
+    }
+  } else if (vl != 0) {
+    st = parse_quantity_general(buf + vp, vl, max_digits, &val);
+  }
+  set_value(r, k, st, val);  // a repeated key overwrites: dict / json.loads last-wins
+}
+
+// The hot walk: one node's row out of shared memory.  Stepping over an entry costs one unaligned
+// word and a few integer ops; key bytes are only compared for candidates, after the loop.
+// Returns false when the row needs the general walk (a 32-bit length escape).
+__device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, NodeResult& r) {
+  r.v01 = r.v23 = 0;
+  r.bits = 0;
+  uint32_t pos, cap_e;
+  if (!row_sections(buf, s, e, &pos, &cap_e)) {
+    r.bits = R_MALFORMED;
+    return true;
+  }
+  uint32_t cand = 0, cand_kp = 0;  // pending candidate: bit 0 valid, bits 1..2 key, bits 3.. value length
+  while (pos < cap_e) {
+    if (cap_e - pos < 2) {
+      r.bits |= R_MALFORMED;
+      break;
+    }
+    const uint32_t w = ld32u(buf, pos);
+    const uint32_t kl = w & 0xFFu, vl = (w >> 8) & 0xFFu;
+    if (kl == 255u || vl == 255u) return false;
+    const uint32_t kp = pos + 2, next = kp + kl + vl;
+    if (next > cap_e) {
+      r.bits |= R_MALFORMED;
+      break;
+    }
+    const uint32_t sig = (kl << 16) | (w >> 16);  // key length and first two bytes
+    const int k = sig == ((14u << 16) | pack4("nv", 0, 2)) ? 0 : sig == ((11u << 16) | pack4("am", 0, 2)) ? 1
+                : sig == ((18u << 16) | pack4("gp", 0, 2)) ? 2 : sig == ((13u << 16) | pack4("in", 0, 2)) ? 3 : -1;
+    if (k >= 0) {
+      if (cand) resolve_candidate(buf, cand, cand_kp, max_digits, r);  // a second candidate in one row: rare
+      cand = 1u | ((uint32_t)k << 1) | (vl << 3);
+      cand_kp = kp;
+    }
+    pos = next;
+  }
+  if (cand) resolve_candidate(buf, cand, cand_kp, max_digits, r);
+  pos = cap_e;
+  while (pos < e) {
+    if (e - pos < 2) {
+      r.bits |= R_MALFORMED;
+      break;
+    }
+    const uint32_t w = ld32u(buf, pos);
+    const uint32_t tl = w & 0xFFu, sl = (w >> 8) & 0xFFu;
+    if (tl == 255u || sl == 255u) return false;
+    const uint32_t kp = pos + 2, next = kp + tl + sl;
+    if (next > e) {
+      r.bits |= R_MALFORMED;
+      break;
+    }
+    if ((w & 0xFFFFu) == (5u | (4u << 8)) && (w >> 16) == pack4("Re", 0, 2) && ld32u(buf, kp + 2) == pack4("adyT", 0, 4) &&
+        (ld32u(buf, kp + 6) & 0xFFFFFFu) == pack4("rue", 0, 3)) {
+      r.bits |= R_READY;  // first hit returns (check-gpu-node.py:176-177)
+      break;
+    }
+    pos = next;
+  }
+  return true;
 }
 
 // 128-bit accumulate of a signed 64-bit addend into (lo, hi); exact under concurrent callers.
@@ -378,46 +525,114 @@ __device__ __forceinline__ void acc128_add(unsigned long long* lo, unsigned long
 }
 
 // ------------------------------------------------------------------------------------------------
-// The kernel.  TN nodes per tile; 2*TN walker threads + one producer warp.
+// Decoupled look-back, 512 tiles wide.  One warp; lane l reads the 16 aggregates of tiles
+// [g + 16 l, g + 16 l + 16) of the aligned 512-tile group g below `t`, and the inclusive prefix at the
+// end of that span.  The nearest valid inclusive prefix (highest lane) ends the search; the lanes
+// above it add their aggregates.  Width matters more than depth here: the prefix front can advance
+// by at most one window per global round trip, so a 32-wide look-back caps the whole kernel at
+// ~20 tiles/us, far below what the memory system feeds.
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t lookback(const Params& p, int t, uint32_t total, int lane) {
+  const uint32_t tag = p.epoch & kEpochMask;
+  if (lane == 0) st_volatile_u32(p.agg + t, (tag << 10) | total);
+  uint32_t excl = 0;
+  int hi = t;  // tiles [0, hi) still to be accounted for
+  while (hi > 0) {
+    const int g0 = (hi - 1) & ~(kLookbackWindow - 1);
+    const int base = g0 + kLookbackSpan * lane;
+    const int need = min(max(hi - base, 0), kLookbackSpan);
+    uint32_t sum, incv = 0;
+    int top;  // highest lane holding a valid inclusive prefix, -1 if none
+    bool good;
+    do {
+      sum = 0;
+      bool ok = true;
+      if (need > 0) {
+#pragma unroll
+        for (int q = 0; q < kLookbackSpan / 4; q++) {
+          const uint4 a = ld_volatile_v4(p.agg + base + 4 * q);
+          const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+          for (int k = 0; k < 4; k++) {
+            if (4 * q + k < need) {
+              ok = ok && (w[k] >> 10) == tag;
+              sum += w[k] & 1023u;
+            }
+          }
+        }
+      }
+      bool has_inc = false;
+      if (need == kLookbackSpan) {
+        const unsigned long long d = ld_volatile_u64(p.inc + base + kLookbackSpan - 1);
+        has_inc = (uint32_t)(d >> 32) == tag;
+        incv = (uint32_t)d;
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, has_inc);
+      top = m ? 31 - __clz(m) : -1;
+      good = lane > top ? ok : true;
+    } while (!__all_sync(0xFFFFFFFFu, good));
+    excl += __reduce_add_sync(0xFFFFFFFFu, lane > top ? sum : (lane == top ? incv : 0u));
+    if (top >= 0) break;
+    hi = g0;
+  }
+  if (lane == 0) st_volatile_u64(p.inc + t, ((unsigned long long)tag << 32) | (excl + total));
+  return excl;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The kernel.  TN nodes per tile, one thread per node.  Warps: TN/32 walkers, 1 producer, 2 scan.
+// ------------------------------------------------------------------------------------------------
+constexpr int kRing = 3;  // a tile's records are written kRing-1 iterations after it was walked
+enum { P_GPU = 0, P_READY, P_DEFERRED, P_MALFORMED, P_KEY0, P_N = 8 };
+
 template <int TN, int STAGES, int STAGE_BYTES>
 struct Smem {
-  alignas(128) uint8_t stage[STAGES][STAGE_BYTES + 16];
+  alignas(128) uint8_t stage[STAGES][STAGE_BYTES + 32];
   alignas(16) uint32_t rp[STAGES][TN + 8];
-  alignas(8) uint64_t full[STAGES];
-  uint64_t empty[STAGES];
+  alignas(8) uint64_t full[STAGES];  // producer/TMA -> walkers: the stage holds a tile
+  uint64_t empty[STAGES];            // walkers -> producer: every walker warp is done with the stage
+  uint64_t cnt_full[kRing];          // walkers -> scan warp: per-warp partial counts of a tile are in part[]
+  uint64_t pref_full[kRing];         // scan warp -> walkers: output positions are in warp_base[]
   unsigned long long acc[GNC_N_COUNTS];
   int tile[STAGES];
   uint32_t lo[STAGES];
-  uint32_t hi[STAGES];          // rows of the tile must end at or before this byte
-  uint32_t direct[STAGES];      // 1: tile too large to stage, walkers read global memory
-  uint32_t cond_bits[2][TN / 32];
-  uint32_t cond_bad[2][TN / 32];
-  uint32_t warp_cnt[TN / 32];
-  uint32_t tile_base;
+  uint32_t hi[STAGES];      // rows of the tile must end at or before this byte
+  uint32_t direct[STAGES];  // 1: tile too large to stage, rows are read from global memory
+  int part[kRing][TN / 32][P_N];
+  uint32_t warp_base[kRing][TN / 32];
+  int scan_tile[kRing];
+  alignas(8) uint2 stash_vals[kRing][TN];  // int16 x 4 per node
+  uint32_t stash_meta[kRing][TN];          // bit 0 GPU node, bit 1 wide, bits 2.. rank in warp
 };
 
+template <int TN>
+__host__ __device__ constexpr int cta_threads() { return TN + 96; }
+
 template <int TN, int STAGES, int STAGE_BYTES, int MIN_CTAS>
-__global__ void __launch_bounds__(2 * TN + 32, MIN_CTAS) classify_kernel(const __grid_constant__ Params p) {
+__global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(const __grid_constant__ Params p) {
   using S = Smem<TN, STAGES, STAGE_BYTES>;
   extern __shared__ __align__(128) uint8_t smem_raw[];
   S& sm = *reinterpret_cast<S*>(smem_raw);
-  constexpr int kWalkers = 2 * TN;
-  constexpr int kCapWarps = TN / 32;
+  constexpr int kWalkWarps = TN / 32;
+  static_assert(TN % 32 == 0 && kWalkWarps <= 32 && TN < 1024, "one scan-warp lane per walker warp; 10-bit tile counts");
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; s++) {
       mbar_init(&sm.full[s], 1);
-      mbar_init(&sm.empty[s], 1);
+      mbar_init(&sm.empty[s], kWalkWarps);
+    }
+    for (int b = 0; b < kRing; b++) {
+      mbar_init(&sm.cnt_full[b], kWalkWarps);
+      mbar_init(&sm.pref_full[b], 1);
     }
     mbar_init_fence();
   }
   if (tid < GNC_N_COUNTS) sm.acc[tid] = 0;
   __syncthreads();
 
-  if (warp == kWalkers / 32) {
+  if (warp == kWalkWarps) {
     // ------------------------------ producer ------------------------------
     if (lane == 0) {
       for (uint32_t it = 0;; ++it) {
@@ -425,7 +640,7 @@ __global__ void __launch_bounds__(2 * TN + 32, MIN_CTAS) classify_kernel(const _
         const uint32_t ph = (it / STAGES) & 1u;
         const uint32_t tile = atomicAdd(&p.scratch->ticket, 1u);
         if (tile >= p.num_tiles) {
-          mbar_wait(&sm.empty[s], ph ^ 1u);
+          mbar_wait_backoff(&sm.empty[s], ph ^ 1u);
           sm.tile[s] = -1;
           mbar_arrive(&sm.full[s]);
           break;
@@ -437,7 +652,7 @@ __global__ void __launch_bounds__(2 * TN + 32, MIN_CTAS) classify_kernel(const _
         const uint32_t bytes = ((hi + 15u) & ~15u) - lo_al;
         const uint32_t rp_bytes = ((cnt + 1) * 4u + 15u) & ~15u;
         const bool direct = hi < lo || hi > p.rows_bytes || bytes > (uint32_t)STAGE_BYTES;
-        mbar_wait(&sm.empty[s], ph ^ 1u);
+        mbar_wait_backoff(&sm.empty[s], ph ^ 1u);
         sm.tile[s] = (int)tile;
         sm.lo[s] = lo_al;
         sm.hi[s] = direct ? (uint32_t)min(p.rows_bytes, (uint64_t)0xFFFFFFFFu) : hi;
@@ -449,16 +664,94 @@ __global__ void __launch_bounds__(2 * TN + 32, MIN_CTAS) classify_kernel(const _
       }
     }
     __syncwarp();  // lanes 1..31 rejoin lane 0 before the CTA-wide barrier below
+  } else if (warp > kWalkWarps) {
+    // ------------------------------ scan warps: this CTA's tile `it` goes to warp it & 1 -------------
+    long long a_gpu = 0, a_ready = 0, a_def = 0, a_bad = 0, a_key[4] = {0, 0, 0, 0};  // lane 0 only
+    for (uint32_t it = warp - kWalkWarps - 1;; it += 2) {
+      const int b = it % kRing;
+      mbar_wait_backoff(&sm.cnt_full[b], (it / kRing) & 1u);
+      const int tile = sm.scan_tile[b];
+      if (tile < 0) break;
+      GNC_T(5, it, gtimer());
+      int part[P_N];
+#pragma unroll
+      for (int q = 0; q < P_N; q++) part[q] = lane < kWalkWarps ? sm.part[b][lane][q] : 0;
+      const uint32_t c = (uint32_t)part[P_GPU];
+      uint32_t incl = c;
+#pragma unroll
+      for (int d = 1; d < kWalkWarps; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, kWalkWarps - 1);
+      const uint32_t excl = lookback(p, tile, total, lane);
+      if (lane < kWalkWarps) sm.warp_base[b][lane] = excl + incl - c;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.pref_full[b]);
+      GNC_T(6, it, gtimer());
+      // the tile's share of the counts block
+      a_gpu += total;
+      a_ready += __reduce_add_sync(0xFFFFFFFFu, part[P_READY]);
+      a_def += __reduce_add_sync(0xFFFFFFFFu, part[P_DEFERRED]);
+      a_bad += __reduce_add_sync(0xFFFFFFFFu, part[P_MALFORMED]);
+#pragma unroll
+      for (int k = 0; k < 4; k++) a_key[k] += __reduce_add_sync(0xFFFFFFFFu, part[P_KEY0 + k]);
+    }
+    if (lane == 0) {
+      atomicAdd(&sm.acc[GNC_C_GPU_NODES], (unsigned long long)a_gpu);
+      atomicAdd(&sm.acc[GNC_C_READY_NODES], (unsigned long long)a_ready);
+      atomicAdd(&sm.acc[GNC_C_DEFERRED], (unsigned long long)a_def);
+      atomicAdd(&sm.acc[GNC_C_MALFORMED], (unsigned long long)a_bad);
+      for (int k = 0; k < 4; k++) acc128_add(&sm.acc[GNC_C_KEY_LO + k], &sm.acc[GNC_C_KEY_HI + k], a_key[k]);
+    }
+    __syncwarp();
   } else {
-    // ------------------------------ walkers -------------------------------
-    const bool cap_role = warp < kCapWarps;
-    const int j = cap_role ? tid : tid - TN;  // node within the tile
-    for (uint32_t it = 0;; ++it) {
+    // ------------------------------ walkers: thread j owns node j of every tile -------------------
+    const int j = tid;
+    uint32_t first_ring[kRing];  // first node of the tiles whose records are still stashed
+#pragma unroll
+    for (int q = 0; q < kRing; q++) first_ring[q] = 0;
+
+    // Write a stashed tile's GPU-node records now that its output positions are known.
+    auto emit_stashed = [&](uint32_t it_e, uint32_t first_e) {
+      const int b = it_e % kRing;
+      mbar_wait(&sm.pref_full[b], (it_e / kRing) & 1u);
+      const uint32_t meta = sm.stash_meta[b][j];
+      bool dropped = false;
+      if (meta & 1u) {
+        const uint32_t pos = sm.warp_base[b][warp] + (meta >> 2);
+        if (pos < p.out_cap) {
+          long long v0, v1, v2, v3;
+          if (meta & 2u) {  // values did not fit 16 bits: read them again from the row
+            SlowRow sr;
+            slow_row(p.rows, __ldg(p.row_ptr + first_e + j), __ldg(p.row_ptr + first_e + j + 1), p.max_digits, &sr);
+            v0 = sr.v[0], v1 = sr.v[1], v2 = sr.v[2], v3 = sr.v[3];
+          } else {
+            const uint2 sv = sm.stash_vals[b][j];
+            v0 = (short)(sv.x & 0xFFFFu), v1 = (short)(sv.x >> 16), v2 = (short)(sv.y & 0xFFFFu), v3 = (short)(sv.y >> 16);
+          }
+          p.gpu_idx[pos] = p.node_base + first_e + j;
+          p.gpu_total[pos] = v0 + v1 + v2 + v3;
+          longlong2* vo = reinterpret_cast<longlong2*>(p.gpu_vals + 4ull * pos);
+          vo[0] = make_longlong2(v0, v1);
+          vo[1] = make_longlong2(v2, v3);
+        } else {
+          dropped = true;
+        }
+      }
+      if (__any_sync(0xFFFFFFFFu, dropped)) {
+        const uint32_t drop_b = __ballot_sync(0xFFFFFFFFu, dropped);
+        if (lane == 0) atomicAdd(&sm.acc[GNC_C_OUT_DROPPED], (unsigned long long)__popc(drop_b));
+      }
+    };
+
+    uint32_t it = 0;
+    for (;; ++it) {
       const int s = it % STAGES;
-      const uint32_t ph = (it / STAGES) & 1u;
-      mbar_wait(&sm.full[s], ph);
+      mbar_wait(&sm.full[s], (it / STAGES) & 1u);
       const int tile = sm.tile[s];
       if (tile < 0) break;
+      if (tid == 0) GNC_T(0, it, gtimer());
       const uint32_t first = (uint32_t)tile * TN;
       const uint32_t cnt = min((uint32_t)TN, p.n_nodes - first);
       const bool live = (uint32_t)j < cnt;
@@ -474,129 +767,98 @@ __global__ void __launch_bounds__(2 * TN + 32, MIN_CTAS) classify_kernel(const _
         bad_ptr = re < rs || re > sm.hi[s] || (!direct && rs < sm.rp[s][0]);
         if (bad_ptr) rs = re = (direct ? 0u : sm.rp[s][0]);
       }
-      CapResult cr;
-      cr.v[0] = cr.v[1] = cr.v[2] = cr.v[3] = 0;
-      cr.present = cr.big = 0;
-      cr.malformed = false;
-      if (cap_role) {
-        if (live) {
-          if (!direct) walk_capacity(sm.stage[s], rs - lo_al, re - lo_al, p.max_digits, cr);
-          else walk_capacity(p.rows, rs, re, p.max_digits, cr);
-        }
-      } else {
-        uint32_t c = 0;
-        if (live) c = direct ? walk_conditions(p.rows, rs, re) : walk_conditions(sm.stage[s], rs - lo_al, re - lo_al);
-        const uint32_t rb = __ballot_sync(0xFFFFFFFFu, c & 1u), bb = __ballot_sync(0xFFFFFFFFu, c & 2u);
-        if (lane == 0) {
-          sm.cond_bits[it & 1][warp - kCapWarps] = rb;
-          sm.cond_bad[it & 1][warp - kCapWarps] = bb;
-        }
+      NodeResult r;
+      r.v01 = r.v23 = r.bits = 0;
+      if (live) {
+        if (direct || !walk_row(sm.stage[s], rs - lo_al, re - lo_al, p.max_digits, r))
+          slow_row_packed(p.rows, rs, re, p.max_digits, &r);
       }
-      named_bar_sync(1, kWalkers);  // every walker is done with stage s; condition bits are visible
-      if (tid == 0) mbar_arrive(&sm.empty[s]);
-      if (!cap_role) continue;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.empty[s]);  // this warp no longer reads the stage
+      if (tid == 0) GNC_T(1, it, gtimer());
 
-      // -------- capacity threads: flags, ordered compaction, counts --------
-      const bool ready = (sm.cond_bits[it & 1][warp] >> lane) & 1u;
-      const bool malformed = cr.malformed || bad_ptr || ((sm.cond_bad[it & 1][warp] >> lane) & 1u);
-      const long long total = cr.v[0] + cr.v[1] + cr.v[2] + cr.v[3];  // |v| < 10^18 each
-      const bool deferred = cr.big != 0;
-      const bool is_gpu = live && !deferred && total > 0;
-      uint32_t f = (is_gpu ? GNC_F_GPU : 0u) | (ready ? GNC_F_READY : 0u) | (deferred ? GNC_F_DEFERRED : 0u) |
-                   (cr.present << 3) | (malformed ? GNC_F_MALFORMED : 0u);
+      // -------- flags, ranks, partial counts; the records go out kRing-1 iterations later --------
+      long long wv[4] = {0, 0, 0, 0};  // exact values of a wide node
+      int v0 = (short)(r.v01 & 0xFFFFu), v1 = (short)(r.v01 >> 16), v2 = (short)(r.v23 & 0xFFFFu), v3 = (short)(r.v23 >> 16);
+      bool positive = v0 + v1 + v2 + v3 > 0;
+      const bool wide = (r.bits & R_WIDE) != 0;
+      if (wide) {
+        SlowRow sr;
+        slow_row(p.rows, rs, re, p.max_digits, &sr);
+        for (int k = 0; k < 4; k++) wv[k] = sr.v[k];
+        positive = wv[0] + wv[1] + wv[2] + wv[3] > 0;  // |v| < 10^18 each
+      }
+      const bool ready = (r.bits & R_READY) != 0;
+      const bool malformed = bad_ptr || (r.bits & R_MALFORMED) != 0;
+      const bool deferred = ((r.bits >> R_BIG_SHIFT) & 0xFu) != 0;
+      const bool is_gpu = live && !deferred && positive;
+      const uint32_t f = (is_gpu ? GNC_F_GPU : 0u) | (ready ? GNC_F_READY : 0u) | (deferred ? GNC_F_DEFERRED : 0u) |
+                         ((r.bits & R_PRESENT) << 3) | (malformed ? GNC_F_MALFORMED : 0u);
+      if (live) p.flags[first + j] = (uint8_t)f;
       const uint32_t gb = __ballot_sync(0xFFFFFFFFu, is_gpu);
       const uint32_t rank = __popc(gb & ((1u << lane) - 1u));
-      if (lane == 0) sm.warp_cnt[warp] = __popc(gb);
-      named_bar_sync(2, TN);
-      if (warp == 0) {
-        uint32_t c = lane < kCapWarps ? sm.warp_cnt[lane] : 0u, incl = c;
-#pragma unroll
-        for (int d = 1; d < kCapWarps; d <<= 1) {
-          uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-          if (lane >= d) incl += t;
-        }
-        const uint32_t tile_total = __shfl_sync(0xFFFFFFFFu, incl, kCapWarps - 1);
-        if (lane < kCapWarps) sm.warp_cnt[lane] = incl - c;  // exclusive offset of each warp
-        // decoupled look-back over earlier tiles' descriptors
-        const unsigned long long tag = (unsigned long long)(p.epoch & kEpochMask) << 32;
-        uint32_t excl = 0;
-        if (tile == 0) {
-          if (lane == 0) st_volatile_u64(p.tile_state, kStatusInclusive | tag | tile_total);
-        } else {
-          if (lane == 0) st_volatile_u64(p.tile_state + tile, kStatusAggregate | tag | tile_total);
-          int look = tile - 1;
-          while (true) {
-            const int t = look - lane;
-            unsigned long long d = kStatusInclusive | tag;  // tiles before 0: inclusive prefix 0
-            if (t >= 0) {
-              do {
-                d = ld_volatile_u64(p.tile_state + t);
-              } while ((d >> 62) == 0 || ((d >> 32) & kEpochMask) != (p.epoch & kEpochMask));
-            }
-            const uint32_t incl_mask = __ballot_sync(0xFFFFFFFFu, (d >> 62) == 2);
-            const int stop = incl_mask ? __ffs(incl_mask) - 1 : 31;  // nearest inclusive descriptor
-            uint32_t v = lane <= stop ? (uint32_t)d : 0u;
-            v = __reduce_add_sync(0xFFFFFFFFu, v);
-            excl += v;
-            if (incl_mask) break;
-            look -= 32;
-          }
-          if (lane == 0) st_volatile_u64(p.tile_state + tile, kStatusInclusive | tag | (excl + tile_total));
-        }
-        if (lane == 0) {
-          sm.tile_base = excl;
-          sm.acc[GNC_C_GPU_NODES] += tile_total;
-        }
-      }
-      named_bar_sync(2, TN);
-      const uint32_t out_pos = sm.tile_base + sm.warp_cnt[warp] + rank;
-      if (live) p.flags[first + j] = (uint8_t)f;
-      bool dropped = false;
-      if (is_gpu) {
-        if (out_pos < p.out_cap) {
-          p.gpu_idx[out_pos] = p.node_base + first + j;
-          p.gpu_total[out_pos] = total;
-          longlong2* vo = reinterpret_cast<longlong2*>(p.gpu_vals + 4ull * out_pos);
-          vo[0] = make_longlong2(cr.v[0], cr.v[1]);
-          vo[1] = make_longlong2(cr.v[2], cr.v[3]);
-        } else {
-          dropped = true;
-        }
-      }
-      // counts: warp-reduced, then a handful of shared-memory atomics per warp
       const uint32_t n_ready = __popc(__ballot_sync(0xFFFFFFFFu, is_gpu && ready));
-      const uint32_t def_b = __ballot_sync(0xFFFFFFFFu, live && deferred);
-      const uint32_t bad_b = __ballot_sync(0xFFFFFFFFu, live && malformed);
-      const uint32_t drop_b = __ballot_sync(0xFFFFFFFFu, dropped);
-      // 32-bit warp sums are exact while every value is within +-2^26
-      const bool wide = is_gpu && ((unsigned long long)(cr.v[0] + (1 << 26)) >> 27 | (unsigned long long)(cr.v[1] + (1 << 26)) >> 27 |
-                                   (unsigned long long)(cr.v[2] + (1 << 26)) >> 27 | (unsigned long long)(cr.v[3] + (1 << 26)) >> 27) != 0;
-      if (!__any_sync(0xFFFFFFFFu, wide)) {
-        int s0 = __reduce_add_sync(0xFFFFFFFFu, is_gpu ? (int)cr.v[0] : 0);
-        int s1 = __reduce_add_sync(0xFFFFFFFFu, is_gpu ? (int)cr.v[1] : 0);
-        int s2 = __reduce_add_sync(0xFFFFFFFFu, is_gpu ? (int)cr.v[2] : 0);
-        int s3 = __reduce_add_sync(0xFFFFFFFFu, is_gpu ? (int)cr.v[3] : 0);
-        if (lane == 0) {
-          acc128_add(&sm.acc[GNC_C_KEY_LO + 0], &sm.acc[GNC_C_KEY_HI + 0], s0);
-          acc128_add(&sm.acc[GNC_C_KEY_LO + 1], &sm.acc[GNC_C_KEY_HI + 1], s1);
-          acc128_add(&sm.acc[GNC_C_KEY_LO + 2], &sm.acc[GNC_C_KEY_HI + 2], s2);
-          acc128_add(&sm.acc[GNC_C_KEY_LO + 3], &sm.acc[GNC_C_KEY_HI + 3], s3);
-        }
-      } else if (is_gpu) {
-#pragma unroll
-        for (int k = 0; k < 4; k++) acc128_add(&sm.acc[GNC_C_KEY_LO + k], &sm.acc[GNC_C_KEY_HI + k], cr.v[k]);
-      }
+      const uint32_t n_def = __popc(__ballot_sync(0xFFFFFFFFu, live && deferred));
+      const uint32_t n_bad = __popc(__ballot_sync(0xFFFFFFFFu, live && malformed));
+      const bool count_narrow = is_gpu && !wide;
+      const int s0 = __reduce_add_sync(0xFFFFFFFFu, count_narrow ? v0 : 0);
+      const int s1 = __reduce_add_sync(0xFFFFFFFFu, count_narrow ? v1 : 0);
+      const int s2 = __reduce_add_sync(0xFFFFFFFFu, count_narrow ? v2 : 0);
+      const int s3 = __reduce_add_sync(0xFFFFFFFFu, count_narrow ? v3 : 0);
+      const int b = it % kRing;
       if (lane == 0) {
-        if (n_ready) atomicAdd(&sm.acc[GNC_C_READY_NODES], (unsigned long long)n_ready);
-        if (def_b) atomicAdd(&sm.acc[GNC_C_DEFERRED], (unsigned long long)__popc(def_b));
-        if (bad_b) atomicAdd(&sm.acc[GNC_C_MALFORMED], (unsigned long long)__popc(bad_b));
-        if (drop_b) atomicAdd(&sm.acc[GNC_C_OUT_DROPPED], (unsigned long long)__popc(drop_b));
+        int* pp = sm.part[b][warp];
+        pp[P_GPU] = __popc(gb);
+        pp[P_READY] = n_ready;
+        pp[P_DEFERRED] = n_def;
+        pp[P_MALFORMED] = n_bad;
+        pp[P_KEY0 + 0] = s0;
+        pp[P_KEY0 + 1] = s1;
+        pp[P_KEY0 + 2] = s2;
+        pp[P_KEY0 + 3] = s3;
+        if (warp == 0) sm.scan_tile[b] = tile;
+        mbar_arrive(&sm.cnt_full[b]);  // the scan warp can start on this tile
+      }
+      if (is_gpu && wide) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) acc128_add(&sm.acc[GNC_C_KEY_LO + k], &sm.acc[GNC_C_KEY_HI + k], wv[k]);
       }
       if (live && deferred) {
         const uint32_t slot = atomicAdd(&p.scratch->defer_count, 1u);
         if (slot < p.defer_cap) emit_defer(p, first + j, rs, re, slot);
         else atomicAdd(&sm.acc[GNC_C_DEFER_DROPPED], 1ull);
       }
+      if (tid == 0) GNC_T(2, it, gtimer());
+
+      // the tile walked kRing-1 iterations ago: its positions have had that long to arrive
+      if (it >= kRing - 1) {
+        uint32_t fe = 0;
+#pragma unroll
+        for (int q = 0; q < kRing; q++)
+          if (q == (int)((it + 1) % kRing)) fe = first_ring[q];
+        emit_stashed(it - (kRing - 1), fe);
+      }
+      if (tid == 0) GNC_T(3, it, gtimer());
+      sm.stash_vals[b][j] = make_uint2(r.v01, r.v23);
+      sm.stash_meta[b][j] = (is_gpu ? 1u : 0u) | (wide ? 2u : 0u) | (rank << 2);
+#pragma unroll
+      for (int q = 0; q < kRing; q++)
+        if (q == b) first_ring[q] = first;
+      if (tid == 0) GNC_T(4, it, gtimer());
+    }
+    // drain the ring, then release both scan warps: their next phase completes with no tile
+    for (uint32_t e = it >= kRing - 1 ? it - (kRing - 1) : 0; e < it; ++e) {
+      uint32_t fe = 0;
+#pragma unroll
+      for (int q = 0; q < kRing; q++)
+        if (q == (int)(e % kRing)) fe = first_ring[q];
+      emit_stashed(e, fe);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      if (warp == 0) sm.scan_tile[it % kRing] = sm.scan_tile[(it + 1) % kRing] = -1;
+      mbar_arrive(&sm.cnt_full[it % kRing]);
+      mbar_arrive(&sm.cnt_full[(it + 1) % kRing]);
     }
   }
 

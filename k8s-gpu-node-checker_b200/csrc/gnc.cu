@@ -30,21 +30,21 @@ struct Variant {
 
 template <int TN, int ST, int SB, int MC>
 void launch_variant(const Params& p, int grid, size_t smem, cudaStream_t stream) {
-  gnc::classify_kernel<TN, ST, SB, MC><<<grid, 2 * TN + 32, smem, stream>>>(p);
+  gnc::classify_kernel<TN, ST, SB, MC><<<grid, gnc::cta_threads<TN>(), smem, stream>>>(p);
 }
 template <int TN, int ST, int SB, int MC>
 Variant make_variant(const char* name) {
-  return Variant{name, TN, SB, 2 * TN + 32, sizeof(gnc::Smem<TN, ST, SB>),
+  return Variant{name, TN, SB, gnc::cta_threads<TN>(), sizeof(gnc::Smem<TN, ST, SB>),
                  (const void*)gnc::classify_kernel<TN, ST, SB, MC>, launch_variant<TN, ST, SB, MC>};
 }
 
-// Ordered by preference: the first whose stage holds an average tile with 6 % to spare is used.
+// Ordered by preference: the first whose stage holds an average tile with 5 % to spare is used.
 const Variant kVariants[] = {
-    make_variant<256, 2, 56320, 2>("t256s2"),
-    make_variant<128, 3, 36864, 2>("t128s3"),
-    make_variant<128, 2, 56320, 2>("t128s2"),
-    make_variant<64, 2, 56320, 2>("t64s2"),
-    make_variant<32, 2, 56320, 2>("t32s2"),
+    make_variant<224, 2, 49664, 2>("t224"),
+    make_variant<160, 2, 49664, 2>("t160"),
+    make_variant<96, 2, 49664, 2>("t96"),
+    make_variant<64, 2, 49664, 2>("t64"),
+    make_variant<32, 2, 49664, 2>("t32"),
 };
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
@@ -77,6 +77,7 @@ struct gnc_ctx {
     cudaEvent_t done = nullptr;    // counts are in h_counts
     cudaEvent_t kernel = nullptr;  // this stage's kernel has finished with the shared scratch
   } hs[2];
+  unsigned long long* trace = nullptr;  // GNC_TRACE builds: set with gnc_debug_trace
   // NCCL (resolved at run time from the already-loaded libnccl.so.2)
   void* nccl_lib = nullptr;
   void* comm = nullptr;
@@ -105,14 +106,14 @@ uint32_t tiles_for(uint32_t n_nodes, int tile_nodes) { return (n_nodes + tile_no
 
 int ensure_scratch(gnc_ctx* c, size_t tiles) {
   if (c->scratch && tiles <= c->scratch_tiles) return GNC_OK;
-  size_t want = std::max<size_t>(tiles, 4096);
+  size_t want = (std::max<size_t>(tiles, 4096) + gnc::kLookbackWindow - 1) / gnc::kLookbackWindow * gnc::kLookbackWindow;
   if (c->scratch) {
     CUDA_TRY(c, cudaDeviceSynchronize());
     CUDA_TRY(c, cudaFree(c->scratch));
     c->scratch = nullptr;
     c->scratch_tiles = 0;
   }
-  size_t bytes = sizeof(ScratchHeader) + want * sizeof(unsigned long long);
+  size_t bytes = sizeof(ScratchHeader) + want * (sizeof(unsigned long long) + sizeof(uint32_t));
   CUDA_TRY(c, cudaMalloc(&c->scratch, bytes));
   CUDA_TRY(c, cudaMemset(c->scratch, 0, bytes));
   CUDA_TRY(c, cudaDeviceSynchronize());
@@ -124,7 +125,7 @@ int pick_variant(const gnc_ctx* c, uint64_t rows_bytes, uint32_t n_nodes) {
   if (c->forced_variant >= 0) return c->forced_variant;
   const double avg = n_nodes ? (double)rows_bytes / n_nodes : 0.0;
   for (int v = 0; v < kNumVariants; v++)
-    if (avg * kVariants[v].tile_nodes * 1.06 + 32 <= kVariants[v].stage_bytes) return v;
+    if (avg * kVariants[v].tile_nodes * 1.05 + 32 <= kVariants[v].stage_bytes) return v;
   return kNumVariants - 1;  // tiles that do not fit are read straight from global memory
 }
 
@@ -219,8 +220,9 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
   rc = ensure_scratch(c, tiles);
   if (rc) return rc;
   c->epoch = (c->epoch + 1) & gnc::kEpochMask;
-  if (c->epoch == 0) {  // epoch wrapped: descriptors from 2^30 launches ago would look current
-    CUDA_TRY(c, cudaMemsetAsync((char*)c->scratch + sizeof(ScratchHeader), 0, c->scratch_tiles * sizeof(unsigned long long), stream));
+  if (c->epoch == 0) {  // epoch wrapped: descriptors from 2^22 launches ago would look current
+    CUDA_TRY(c, cudaMemsetAsync((char*)c->scratch + sizeof(ScratchHeader), 0,
+                                c->scratch_tiles * (sizeof(unsigned long long) + sizeof(uint32_t)), stream));
     c->epoch = 1;
   }
   Params p;
@@ -241,7 +243,12 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
   p.out_cap = out->out_cap;
   p.defer_cap = out->defer ? out->defer_cap : 0;
   p.scratch = (ScratchHeader*)c->scratch;
-  p.tile_state = (unsigned long long*)((char*)c->scratch + sizeof(ScratchHeader));
+  p.inc = (unsigned long long*)((char*)c->scratch + sizeof(ScratchHeader));
+  p.agg = (uint32_t*)(p.inc + c->scratch_tiles);
+  p.trace = nullptr;
+#ifdef GNC_TRACE
+  p.trace = c->trace;
+#endif
   const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(c->sm_count * c->ctas_per_sm[v]));
   var.launch(p, grid, var.smem, stream);
   CUDA_TRY(c, cudaGetLastError());
@@ -262,6 +269,14 @@ int gnc_unicode_tables(const uint32_t** nd_runs, int* n_runs, const uint32_t** s
 }
 
 const char* gnc_last_error(const gnc_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+#ifdef GNC_TRACE
+// Debug builds only: device buffer of 296*64*8 u64 the next launches write phase timestamps into.
+int gnc_debug_trace(gnc_ctx* c, void* device_buffer) {
+  c->trace = (unsigned long long*)device_buffer;
+  return GNC_OK;
+}
+#endif
 
 }  // extern "C"
 

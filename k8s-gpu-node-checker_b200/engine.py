@@ -84,7 +84,6 @@ class FleetResult:
     def total_nodes(self) -> int:             # check-gpu-node.py:275
         return len(self.gpu_idx)
 
-    @property
     def is_ready(self, pos: int) -> bool:
         return bool(self.flags[int(self.gpu_idx[pos]) - self.node_base] & F_READY)
 

@@ -76,7 +76,7 @@ def test_fleet_sizes(clf, g2, kind, n):
     tmpl, rows, truth, _ = g2
     _, tid = synth.fleet(kind, 1, 17, n)
     p = pnl.from_rows([rows[t] for t in tid])
-    got = run_device(clf, p, node_base=1000)
+    got = run_device(clf, p, node_base=1000, defer_cap=1 << 15)
     exp = expected_outputs(truth, tid, node_base=1000)
     assert_same_outputs(got, exp, f"{kind} n={n}")
     ora = po.classify(p.rows, p.row_ptr, n, node_base=1000)
@@ -147,7 +147,7 @@ def test_1m_adversarial_fleet(clf, g2):
     assert fr.exit_code == 0
 
 
-@pytest.mark.parametrize("variant", ["t256s2", "t128s3", "t128s2", "t64s2", "t32s2"])
+@pytest.mark.parametrize("variant", ["t224", "t160", "t96", "t64", "t32"])
 def test_every_kernel_variant(g2, variant, monkeypatch):
     """Each tile shape, on a fleet with rows too large to stage (read straight from global memory)."""
     tmpl, rows, truth, _ = g2
