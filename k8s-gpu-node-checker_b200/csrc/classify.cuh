@@ -204,7 +204,8 @@ __device__ __forceinline__ int classify_cp(uint32_t cp) {
   return d <= 9u ? (int)d : C_OTHER;
 }
 
-__device__ __noinline__ int parse_quantity_general(const uint8_t* s, uint32_t n, int max_digits, long long* out) {
+// Returns (value << 2) | status: nothing is passed by address, so callers keep their state in registers.
+__device__ __noinline__ long long parse_quantity_general(const uint8_t* s, uint32_t n, int max_digits) {
   uint32_t i = 0, sig = 0;
   int phase = 0;  // 0 leading ws, 1 after sign, 2 in digits, 3 after '_', 4 trailing ws
   bool neg = false;
@@ -250,59 +251,7 @@ __device__ __noinline__ int parse_quantity_general(const uint8_t* s, uint32_t n,
   if (phase != 2 && phase != 4) return Q_ABSENT;
   if (max_digits > 0 && digits > (unsigned long long)max_digits) return Q_ABSENT;
   if (sig > 18) return Q_BIG;
-  *out = neg ? -(long long)v : (long long)v;
-  return Q_OK;
-}
-
-// Entry header at `pos` inside [pos, end): lengths, position of the key, first two key bytes.
-struct Entry {
-  uint32_t kl, vl, kp, k01;
-  bool ok;
-};
-__device__ __forceinline__ Entry read_entry(const uint8_t* buf, uint32_t pos, uint32_t end) {
-  Entry e;
-  e.ok = false;
-  e.kl = e.vl = e.kp = e.k01 = 0;
-  if (end - pos < 2) return e;
-  uint32_t w = ld32u(buf, pos);
-  e.kl = w & 0xFFu;
-  e.vl = (w >> 8) & 0xFFu;
-  e.kp = pos + 2;
-  e.k01 = w >> 16;
-  if (e.kl == 255u || e.vl == 255u) {  // 32-bit length escapes
-    if (e.kl == 255u) {
-      if (end - e.kp < 4) return e;
-      e.kl = ld32u(buf, e.kp);
-      e.kp += 4;
-    }
-    if (e.vl == 255u) {
-      if (end - e.kp < 4) return e;
-      e.vl = ld32u(buf, e.kp);
-      e.kp += 4;
-    }
-    e.k01 = ld32u(buf, e.kp) & 0xFFFFu;
-    if ((unsigned long long)e.kl + e.vl > (unsigned long long)(end - e.kp)) return e;
-  } else if (e.kl + e.vl > end - e.kp) {
-    return e;
-  }
-  e.ok = true;
-  return e;
-}
-
-// Row header: capacity section [*cap_b, *cap_e), conditions [*cap_e, e). False if the header is bad.
-__device__ __forceinline__ bool row_sections(const uint8_t* buf, uint32_t s, uint32_t e, uint32_t* cap_b, uint32_t* cap_e) {
-  *cap_b = *cap_e = e;
-  if (e - s < 2) return e == s;
-  uint32_t w = ld32u(buf, s), len = w & 0xFFFFu, p = s + 2;
-  if (len == 0xFFFFu) {
-    if (e - s < 6) return false;
-    len = ld32u(buf, s + 2);
-    p = s + 6;
-  }
-  if (len > e - p) return false;
-  *cap_b = p;
-  *cap_e = p + len;
-  return true;
+  return ((neg ? -(long long)v : (long long)v) << 2) | Q_OK;  // |v| < 10^18 < 2^60
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -334,14 +283,21 @@ __device__ __forceinline__ void set_value(NodeResult& r, int k, int st, long lon
   else r.v01 = (r.v01 & ~m) | x;
 }
 
-// Slow, general, out-of-line walk of one row from a generic pointer: every escape, exact 64-bit
-// values, value-text positions.  Rows with 32-bit length escapes, rows of tiles too large to stage,
-// wide and deferred nodes come here; the hot path below never does.
+// Slow, general, out-of-line walk of one row from a generic pointer, byte by byte: both row forms,
+// any alignment, exact 64-bit values, value-text positions.  Extended rows, rows of tiles too large
+// to stage, wide and deferred nodes come here; the hot path below never does.
 struct SlowRow {
   long long v[4];
   uint32_t off[4], len[4];
   uint32_t bits;  // R_PRESENT / big / R_MALFORMED / R_READY (never R_WIDE)
 };
+
+__constant__ char c_key_text[4][20] = {"nvidia.com/gpu", "amd.com/gpu", "gpu.intel.com/i915", "intel.com/gpu"};
+__constant__ uint32_t c_key_len[4] = {14, 11, 18, 13};
+
+__device__ __forceinline__ uint32_t ldb32(const uint8_t* p) {
+  return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+}
 
 __device__ __noinline__ void slow_row(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, SlowRow* out) {
   for (int k = 0; k < 4; k++) {
@@ -349,63 +305,82 @@ __device__ __noinline__ void slow_row(const uint8_t* buf, uint32_t s, uint32_t e
     out->off[k] = 0xFFFFFFFFu;
     out->len[k] = 0;
   }
-  uint32_t bits = 0, pos, cap_e;
-  if (!row_sections(buf, s, e, &pos, &cap_e)) {
+  out->bits = 0;
+  if (e - s < 2) {
+    if (e != s) out->bits = R_MALFORMED;
+    return;
+  }
+  const bool ext = buf[s] == 0xFF;
+  unsigned long long n_cap, n_cond, tab, stride;
+  if (ext) {
+    if (e - s < 12) {
+      out->bits = R_MALFORMED;
+      return;
+    }
+    n_cap = ldb32(buf + s + 4);
+    n_cond = ldb32(buf + s + 8);
+    tab = (unsigned long long)s + 12;
+    stride = 8;
+  } else {
+    n_cap = buf[s];
+    n_cond = buf[s + 1];
+    tab = (unsigned long long)s + 2;
+    stride = 2;
+  }
+  const unsigned long long n = n_cap + n_cond;
+  unsigned long long off = tab + stride * n;
+  if (off > e) {
     out->bits = R_MALFORMED;
     return;
   }
-  while (pos < cap_e) {
-    Entry en = read_entry(buf, pos, cap_e);
-    if (!en.ok) {
+  uint32_t bits = 0;
+  for (unsigned long long i = 0; i < n; i++) {
+    const unsigned long long kl = ext ? ldb32(buf + tab + 8 * i) : buf[tab + 2 * i];
+    const unsigned long long vl = ext ? ldb32(buf + tab + 8 * i + 4) : buf[tab + 2 * i + 1];
+    if (off + kl + vl > e) {
       bits |= R_MALFORMED;
       break;
     }
-    int k = -1;
-    if (en.kl == 14 && en.k01 == pack4("nv", 0, 2) && key_tail_eq<14>(buf, en.kp, "nvidia.com/gpu")) k = 0;
-    if (en.kl == 11 && en.k01 == pack4("am", 0, 2) && key_tail_eq<11>(buf, en.kp, "amd.com/gpu")) k = 1;
-    if (en.kl == 18 && en.k01 == pack4("gp", 0, 2) && key_tail_eq<18>(buf, en.kp, "gpu.intel.com/i915")) k = 2;
-    if (en.kl == 13 && en.k01 == pack4("in", 0, 2) && key_tail_eq<13>(buf, en.kp, "intel.com/gpu")) k = 3;
-    const uint32_t vp = en.kp + en.kl;
-    if (k >= 0) {  // a repeated key overwrites: dict / json.loads last-wins
-      long long val = 0;
-      const int st = en.vl ? parse_quantity_general(buf + vp, en.vl, max_digits, &val) : Q_ABSENT;
-      const uint32_t bit = 1u << k;
-      bits = (bits & ~(bit | (bit << R_BIG_SHIFT))) | (st != Q_ABSENT ? bit : 0u) | (st == Q_BIG ? bit << R_BIG_SHIFT : 0u);
-      out->v[k] = st == Q_OK ? val : 0;
-      out->off[k] = st == Q_ABSENT ? 0xFFFFFFFFu : vp;
-      out->len[k] = st == Q_ABSENT ? 0u : en.vl;
-    }
-    pos = vp + en.vl;
-  }
-  pos = cap_e;
-  while (pos < e) {
-    Entry en = read_entry(buf, pos, e);
-    if (!en.ok) {
-      bits |= R_MALFORMED;
-      break;
-    }
-    if (en.kl == 5 && en.vl == 4 && en.k01 == pack4("Re", 0, 2) && ld32u(buf, en.kp + 2) == pack4("adyT", 0, 4) &&
-        (ld32u(buf, en.kp + 6) & 0xFFFFFFu) == pack4("rue", 0, 3)) {
+    const uint8_t* key = buf + off;
+    const uint8_t* val = key + kl;
+    if (i < n_cap) {
+      for (int k = 0; k < 4; k++) {
+        if (kl != c_key_len[k]) continue;
+        bool eq = true;
+        for (uint32_t q = 0; q < c_key_len[k]; q++) eq = eq && key[q] == (uint8_t)c_key_text[k][q];
+        if (!eq) continue;
+        // a repeated key overwrites: dict / json.loads last-wins
+        const long long pq = vl ? parse_quantity_general(val, (uint32_t)vl, max_digits) : (long long)Q_ABSENT;
+        const int st = (int)(pq & 3);
+        const long long x = pq >> 2;
+        const uint32_t bit = 1u << k;
+        bits = (bits & ~(bit | (bit << R_BIG_SHIFT))) | (st != Q_ABSENT ? bit : 0u) | (st == Q_BIG ? bit << R_BIG_SHIFT : 0u);
+        out->v[k] = st == Q_OK ? x : 0;
+        out->off[k] = st == Q_ABSENT ? 0xFFFFFFFFu : (uint32_t)(off + kl);
+        out->len[k] = st == Q_ABSENT ? 0u : (uint32_t)vl;
+      }
+    } else if (kl == 5 && vl == 4 && key[0] == 'R' && key[1] == 'e' && key[2] == 'a' && key[3] == 'd' && key[4] == 'y' &&
+               val[0] == 'T' && val[1] == 'r' && val[2] == 'u' && val[3] == 'e') {
       bits |= R_READY;  // first hit returns (check-gpu-node.py:176-177)
       break;
     }
-    pos = en.kp + en.kl + en.vl;
+    off += kl + vl;
   }
   out->bits = bits;
 }
 
-__device__ __noinline__ void slow_row_packed(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, NodeResult* r) {
+__device__ __noinline__ uint3 slow_row_packed(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits) {
   SlowRow sr;
   slow_row(buf, s, e, max_digits, &sr);
-  r->v01 = r->v23 = 0;
-  r->bits = sr.bits;
+  uint3 r = make_uint3(0u, 0u, sr.bits);  // v01, v23, bits
   for (int k = 0; k < 4; k++) {
     const bool fits = (unsigned long long)(sr.v[k] + 32768) < 65536ull;
-    if (!fits) r->bits |= R_WIDE;
+    if (!fits) r.z |= R_WIDE;
     const uint32_t x = fits ? ((uint32_t)sr.v[k] & 0xFFFFu) : 0u;
-    if (k & 2) r->v23 |= x << ((k & 1) << 4);
-    else r->v01 |= x << ((k & 1) << 4);
+    if (k & 2) r.y |= x << ((k & 1) << 4);
+    else r.x |= x << ((k & 1) << 4);
   }
+  return r;
 }
 
 __device__ __noinline__ void emit_defer(const Params& p, uint32_t node, uint32_t s, uint32_t e, uint32_t slot) {
@@ -420,97 +395,118 @@ __device__ __noinline__ void emit_defer(const Params& p, uint32_t node, uint32_t
   p.defer[slot] = rec;
 }
 
-// A key candidate (length and first two bytes fit one of the four keys): compare the rest of the key
-// with per-key constants picked by select (no divergence between lanes holding different keys) and
-// parse the value.  One call per node in the common case, with the warp converged.
-__device__ __forceinline__ void resolve_candidate(const uint8_t* buf, uint32_t cand, uint32_t kp, int max_digits, NodeResult& r) {
-  const int k = (cand >> 1) & 3;
-  const uint32_t vl = cand >> 3;
-  // key bytes [2, 18): words at +2, +6, +10, +14
-  const uint32_t e0 = k == 0 ? pack4("idia", 0, 4) : k == 1 ? pack4("d.co", 0, 4) : k == 2 ? pack4("u.in", 0, 4) : pack4("tel.", 0, 4);
-  const uint32_t e1 = k == 0 ? pack4(".com", 0, 4) : k == 1 ? pack4("m/gp", 0, 4) : k == 2 ? pack4("tel.", 0, 4) : pack4("com/", 0, 4);
-  const uint32_t e2 = k == 0 ? pack4("/gpu", 0, 4) : k == 1 ? pack4("u", 0, 1) : k == 2 ? pack4("com/", 0, 4) : pack4("gpu", 0, 3);
-  const uint32_t m2 = k == 1 ? 0xFFu : k == 3 ? 0xFFFFFFu : 0xFFFFFFFFu;
-  const uint32_t e3 = k == 2 ? pack4("i915", 0, 4) : 0u;
-  const uint32_t m3 = k == 2 ? 0xFFFFFFFFu : 0u;
-  const bool eq = ld32u(buf, kp + 2) == e0 && ld32u(buf, kp + 6) == e1 && (ld32u(buf, kp + 10) & m2) == e2 &&
-                  (ld32u(buf, kp + 14) & m3) == e3;
+// A real key (length and first four bytes match): compare the rest of the key against per-key
+// constants picked by select -- no divergence between lanes holding different keys -- and parse the
+// value.  `rec` is (row-relative text offset << 16) | vlen << 8 | klen.
+__device__ __forceinline__ void resolve_key(const uint8_t* buf, uint32_t s, uint32_t rec, int max_digits, NodeResult& r) {
+  const uint32_t kl = rec & 0xFFu, vl = (rec >> 8) & 0xFFu, kp = s + (rec >> 16);
+  const int k = kl == 14u ? 0 : kl == 11u ? 1 : kl == 18u ? 2 : 3;
+  const uint32_t e1 = k == 0 ? pack4("ia.c", 0, 4) : k == 1 ? pack4("com/", 0, 4) : k == 2 ? pack4("inte", 0, 4) : pack4("l.co", 0, 4);
+  const uint32_t e2 = k == 0 ? pack4("om/g", 0, 4) : k == 1 ? pack4("gpu", 0, 3) : k == 2 ? pack4("l.co", 0, 4) : pack4("m/gp", 0, 4);
+  const uint32_t m2 = k == 1 ? 0xFFFFFFu : 0xFFFFFFFFu;
+  const uint32_t e3 = k == 0 ? pack4("pu", 0, 2) : k == 1 ? 0u : k == 2 ? pack4("m/i9", 0, 4) : pack4("u", 0, 1);
+  const uint32_t m3 = k == 0 ? 0xFFFFu : k == 1 ? 0u : k == 2 ? 0xFFFFFFFFu : 0xFFu;
+  const uint32_t m4 = k == 2 ? 0xFFFFu : 0u;
+  const bool eq = ld32u(buf, kp + 4) == e1 && (ld32u(buf, kp + 8) & m2) == e2 && (ld32u(buf, kp + 12) & m3) == e3 &&
+                  (ld32u(buf, kp + 16) & m4) == (pack4("15", 0, 2) & m4);
   if (!eq) return;
-  const uint32_t kl = k == 0 ? 14u : k == 1 ? 11u : k == 2 ? 18u : 13u;
   const uint32_t vp = kp + kl;
-  int st = Q_ABSENT;
-  long long val = 0;
+  long long pq = Q_ABSENT;
   if (vl == 1) {
     const uint32_t d = (uint32_t)buf[vp] - '0';
-    if (d <= 9u) {
-      st = Q_OK;
-      val = d;
-    } else {
-      st = parse_quantity_general(buf + vp, 1, max_digits, &val);
-    }
+    pq = d <= 9u ? (long long)((d << 2) | Q_OK) : parse_quantity_general(buf + vp, 1, max_digits);
   } else if (vl != 0) {
-    st = parse_quantity_general(buf + vp, vl, max_digits, &val);
+    pq = parse_quantity_general(buf + vp, vl, max_digits);
   }
-  set_value(r, k, st, val);  // a repeated key overwrites: dict / json.loads last-wins
+  set_value(r, k, (int)(pq & 3), pq >> 2);  // a repeated key overwrites: dict / json.loads last-wins
 }
 
-// The hot walk: one node's row out of shared memory.  Stepping over an entry costs one unaligned
-// word and a few integer ops; key bytes are only compared for candidates, after the loop.
-// Returns false when the row needs the general walk (a 32-bit length escape).
+// The hot walk: one node's row out of shared memory.
+//  1. scan the length table, two entries per 32-bit word, with no branch per entry: running text
+//     offset by integer adds; entries that could matter (a capacity key of length 11/13/14/18, a
+//     condition of lengths 5 and 4) are pushed into small shift registers;
+//  2. look at the candidates' text, oldest first.  Every lane has about the same number of
+//     candidates, so the warp stays converged here whatever position the keys had in the rows.
+// Returns false when the row needs the general walk (extended form, a 0xFF byte in the table,
+// misaligned or >= 64 KB row, more candidates than the registers hold).
 __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, NodeResult& r) {
   r.v01 = r.v23 = 0;
   r.bits = 0;
-  uint32_t pos, cap_e;
-  if (!row_sections(buf, s, e, &pos, &cap_e)) {
+  if (e - s < 2) {
+    if (e != s) r.bits = R_MALFORMED;
+    return true;
+  }
+  if ((s & 3u) || e - s >= 65536u) return false;
+  const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + s);
+  uint32_t w = wp[0];
+  const uint32_t n_cap = w & 0xFFu, n_cond = (w >> 8) & 0xFFu;
+  if (n_cap == 0xFFu) return false;
+  const uint32_t n = n_cap + n_cond;
+  uint32_t rel = 2u + 2u * n;  // row-relative offset of the text of the next entry
+  if (s + rel > e) {
     r.bits = R_MALFORMED;
     return true;
   }
-  uint32_t cand = 0, cand_kp = 0;  // pending candidate: bit 0 valid, bits 1..2 key, bits 3.. value length
-  while (pos < cap_e) {
-    if (cap_e - pos < 2) {
-      r.bits |= R_MALFORMED;
-      break;
+  uint32_t k0 = 0, k1 = 0, k2 = 0, k3 = 0, nk = 0;  // capacity candidates, k0 newest
+  uint32_t q0 = 0, q1 = 0, nq = 0;                  // condition candidates, q0 newest
+  uint32_t ff = __vcmpeq4(w | 0x0000FFFFu, 0xFFFFFFFFu) & 0xFFFF0000u;  // a 0xFF length byte anywhere
+  auto step = [&](uint32_t hv, uint32_t idx) {
+    const uint32_t kl = hv & 0xFFu, len = kl + (hv >> 8);
+    const bool valid = idx < n, in_cap = idx < n_cap;
+    const bool ccap = valid && in_cap && ((0x46800u >> kl) & 1u) && kl < 32u;
+    const bool ccond = valid && !in_cap && hv == (5u | (4u << 8));
+    const uint32_t rec = (rel << 16) | hv;
+    if (ccap) {
+      k3 = k2, k2 = k1, k1 = k0, k0 = rec;
+      ++nk;
     }
-    const uint32_t w = ld32u(buf, pos);
-    const uint32_t kl = w & 0xFFu, vl = (w >> 8) & 0xFFu;
-    if (kl == 255u || vl == 255u) return false;
-    const uint32_t kp = pos + 2, next = kp + kl + vl;
-    if (next > cap_e) {
-      r.bits |= R_MALFORMED;
-      break;
+    if (ccond) {
+      q1 = q0, q0 = rec;
+      ++nq;
     }
-    const uint32_t sig = (kl << 16) | (w >> 16);  // key length and first two bytes
-    const int k = sig == ((14u << 16) | pack4("nv", 0, 2)) ? 0 : sig == ((11u << 16) | pack4("am", 0, 2)) ? 1
-                : sig == ((18u << 16) | pack4("gp", 0, 2)) ? 2 : sig == ((13u << 16) | pack4("in", 0, 2)) ? 3 : -1;
-    if (k >= 0) {
-      if (cand) resolve_candidate(buf, cand, cand_kp, max_digits, r);  // a second candidate in one row: rare
-      cand = 1u | ((uint32_t)k << 1) | (vl << 3);
-      cand_kp = kp;
-    }
-    pos = next;
+    rel += valid ? len : 0u;
+  };
+  step(w >> 16, 0);
+  for (uint32_t j = 1; 2 * j - 1 < n; ++j) {
+    w = wp[j];
+    ff |= __vcmpeq4(w, 0xFFFFFFFFu);
+    step(w & 0xFFFFu, 2 * j - 1);
+    step(w >> 16, 2 * j);
   }
-  if (cand) resolve_candidate(buf, cand, cand_kp, max_digits, r);
-  pos = cap_e;
-  while (pos < e) {
-    if (e - pos < 2) {
-      r.bits |= R_MALFORMED;
-      break;
+  if (ff || nk > 4u || nq > 2u || rel >= 65536u) return false;
+  const uint32_t row_len = e - s;
+  bool stop = false;
+  // capacity candidates, oldest first: bounds, then the first four key bytes
+#pragma unroll
+  for (int i = 3; i >= 0; --i) {
+    const uint32_t rec = i == 3 ? k3 : i == 2 ? k2 : i == 1 ? k1 : k0;
+    if ((uint32_t)i < nk && !stop) {
+      const uint32_t kl = rec & 0xFFu;
+      if ((rec >> 16) + kl + ((rec >> 8) & 0xFFu) > row_len) {
+        r.bits |= R_MALFORMED;  // the entry's text runs past the row: nothing after it counts
+        stop = true;
+      } else {
+        const uint32_t e0 = kl == 14u ? pack4("nvid", 0, 4) : kl == 11u ? pack4("amd.", 0, 4) : kl == 18u ? pack4("gpu.", 0, 4) : pack4("inte", 0, 4);
+        if (ld32u(buf, s + (rec >> 16)) == e0) resolve_key(buf, s, rec, max_digits, r);
+      }
     }
-    const uint32_t w = ld32u(buf, pos);
-    const uint32_t tl = w & 0xFFu, sl = (w >> 8) & 0xFFu;
-    if (tl == 255u || sl == 255u) return false;
-    const uint32_t kp = pos + 2, next = kp + tl + sl;
-    if (next > e) {
-      r.bits |= R_MALFORMED;
-      break;
-    }
-    if ((w & 0xFFFFu) == (5u | (4u << 8)) && (w >> 16) == pack4("Re", 0, 2) && ld32u(buf, kp + 2) == pack4("adyT", 0, 4) &&
-        (ld32u(buf, kp + 6) & 0xFFFFFFu) == pack4("rue", 0, 3)) {
-      r.bits |= R_READY;  // first hit returns (check-gpu-node.py:176-177)
-      break;
-    }
-    pos = next;
   }
+  // condition candidates, oldest first: the first (Ready, True) ends the walk (check-gpu-node.py:176-177)
+#pragma unroll
+  for (int i = 1; i >= 0; --i) {
+    const uint32_t rec = i == 1 ? q1 : q0;
+    if ((uint32_t)i < nq && !stop) {
+      const uint32_t kp = s + (rec >> 16);
+      if ((rec >> 16) + 9u > row_len) {
+        r.bits |= R_MALFORMED;
+        stop = true;
+      } else if (ld32u(buf, kp) == pack4("Read", 0, 4) && ld32u(buf, kp + 4) == pack4("yTru", 0, 4) && (ld32u(buf, kp + 8) & 0xFFu) == 'e') {
+        r.bits |= R_READY;
+        stop = true;
+      }
+    }
+  }
+  if (!stop && rel > row_len) r.bits |= R_MALFORMED;  // some entry's text ran past the row
   return true;
 }
 
@@ -533,8 +529,7 @@ __device__ __forceinline__ void acc128_add(unsigned long long* lo, unsigned long
 // ~20 tiles/us, far below what the memory system feeds.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t lookback(const Params& p, int t, uint32_t total, int lane) {
-  const uint32_t tag = p.epoch & kEpochMask;
-  if (lane == 0) st_volatile_u32(p.agg + t, (tag << 10) | total);
+  const uint32_t tag = p.epoch & kEpochMask;  // agg[t] was published by the walkers the moment the tile was counted
   uint32_t excl = 0;
   int hi = t;  // tiles [0, hi) still to be accounted for
   while (hi > 0) {
@@ -582,7 +577,7 @@ __device__ __forceinline__ uint32_t lookback(const Params& p, int t, uint32_t to
 // ------------------------------------------------------------------------------------------------
 // The kernel.  TN nodes per tile, one thread per node.  Warps: TN/32 walkers, 1 producer, 2 scan.
 // ------------------------------------------------------------------------------------------------
-constexpr int kRing = 3;  // a tile's records are written kRing-1 iterations after it was walked
+constexpr int kRing = 6;  // a tile's records are written kRing-1 iterations after it was walked
 enum { P_GPU = 0, P_READY, P_DEFERRED, P_MALFORMED, P_KEY0, P_N = 8 };
 
 template <int TN, int STAGES, int STAGE_BYTES>
@@ -601,8 +596,9 @@ struct Smem {
   int part[kRing][TN / 32][P_N];
   uint32_t warp_base[kRing][TN / 32];
   int scan_tile[kRing];
+  uint32_t tile_cnt[kRing];  // [31:16] walker warps done with the tile, [15:0] GPU nodes counted so far
   alignas(8) uint2 stash_vals[kRing][TN];  // int16 x 4 per node
-  uint32_t stash_meta[kRing][TN];          // bit 0 GPU node, bit 1 wide, bits 2.. rank in warp
+  uint8_t stash_meta[kRing][TN];           // bit 0 GPU node, bit 1 wide, bits 2..6 rank in warp
 };
 
 template <int TN>
@@ -630,6 +626,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
     mbar_init_fence();
   }
   if (tid < GNC_N_COUNTS) sm.acc[tid] = 0;
+  if (tid < kRing) sm.tile_cnt[tid] = 0;
   __syncthreads();
 
   if (warp == kWalkWarps) {
@@ -708,9 +705,9 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   } else {
     // ------------------------------ walkers: thread j owns node j of every tile -------------------
     const int j = tid;
-    uint32_t first_ring[kRing];  // first node of the tiles whose records are still stashed
+    uint32_t lag_first[kRing - 1];  // first node of the tiles walked 1 .. kRing-1 iterations ago (registers: static indices only)
 #pragma unroll
-    for (int q = 0; q < kRing; q++) first_ring[q] = 0;
+    for (int q = 0; q < kRing - 1; q++) lag_first[q] = 0;
 
     // Write a stashed tile's GPU-node records now that its output positions are known.
     auto emit_stashed = [&](uint32_t it_e, uint32_t first_e) {
@@ -770,15 +767,17 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       NodeResult r;
       r.v01 = r.v23 = r.bits = 0;
       if (live) {
-        if (direct || !walk_row(sm.stage[s], rs - lo_al, re - lo_al, p.max_digits, r))
-          slow_row_packed(p.rows, rs, re, p.max_digits, &r);
+        if (direct || !walk_row(sm.stage[s], rs - lo_al, re - lo_al, p.max_digits, r)) {
+          const uint3 q = slow_row_packed(p.rows, rs, re, p.max_digits);
+          r.v01 = q.x, r.v23 = q.y, r.bits = q.z;
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.empty[s]);  // this warp no longer reads the stage
       if (tid == 0) GNC_T(1, it, gtimer());
 
       // -------- flags, ranks, partial counts; the records go out kRing-1 iterations later --------
-      long long wv[4] = {0, 0, 0, 0};  // exact values of a wide node
+      long long wv[4] = {0, 0, 0, 0};  // exact values of a wide node (rare)
       int v0 = (short)(r.v01 & 0xFFFFu), v1 = (short)(r.v01 >> 16), v2 = (short)(r.v23 & 0xFFFFu), v3 = (short)(r.v23 >> 16);
       bool positive = v0 + v1 + v2 + v3 > 0;
       const bool wide = (r.bits & R_WIDE) != 0;
@@ -817,6 +816,13 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         pp[P_KEY0 + 2] = s2;
         pp[P_KEY0 + 3] = s3;
         if (warp == 0) sm.scan_tile[b] = tile;
+        // the last warp to count its share publishes the tile's aggregate at once: other CTAs'
+        // look-backs must never wait for this CTA's scan warp to get round to the tile
+        const uint32_t old = atomicAdd(&sm.tile_cnt[b], (uint32_t)__popc(gb) | (1u << 16));
+        if ((old >> 16) == (uint32_t)kWalkWarps - 1) {
+          sm.tile_cnt[b] = 0;
+          st_volatile_u32(p.agg + tile, ((p.epoch & kEpochMask) << 10) | ((old & 0xFFFFu) + (uint32_t)__popc(gb)));
+        }
         mbar_arrive(&sm.cnt_full[b]);  // the scan warp can start on this tile
       }
       if (is_gpu && wide) {
@@ -831,29 +837,19 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       if (tid == 0) GNC_T(2, it, gtimer());
 
       // the tile walked kRing-1 iterations ago: its positions have had that long to arrive
-      if (it >= kRing - 1) {
-        uint32_t fe = 0;
-#pragma unroll
-        for (int q = 0; q < kRing; q++)
-          if (q == (int)((it + 1) % kRing)) fe = first_ring[q];
-        emit_stashed(it - (kRing - 1), fe);
-      }
+      if (it >= kRing - 1) emit_stashed(it - (kRing - 1), lag_first[kRing - 2]);
       if (tid == 0) GNC_T(3, it, gtimer());
       sm.stash_vals[b][j] = make_uint2(r.v01, r.v23);
-      sm.stash_meta[b][j] = (is_gpu ? 1u : 0u) | (wide ? 2u : 0u) | (rank << 2);
+      sm.stash_meta[b][j] = (uint8_t)((is_gpu ? 1u : 0u) | (wide ? 2u : 0u) | (rank << 2));
 #pragma unroll
-      for (int q = 0; q < kRing; q++)
-        if (q == b) first_ring[q] = first;
+      for (int q = kRing - 2; q > 0; q--) lag_first[q] = lag_first[q - 1];
+      lag_first[0] = first;
       if (tid == 0) GNC_T(4, it, gtimer());
     }
     // drain the ring, then release both scan warps: their next phase completes with no tile
-    for (uint32_t e = it >= kRing - 1 ? it - (kRing - 1) : 0; e < it; ++e) {
-      uint32_t fe = 0;
 #pragma unroll
-      for (int q = 0; q < kRing; q++)
-        if (q == (int)(e % kRing)) fe = first_ring[q];
-      emit_stashed(e, fe);
-    }
+    for (int q = kRing - 2; q >= 0; q--)
+      if (it >= (uint32_t)q + 1) emit_stashed(it - (q + 1), lag_first[q]);
     __syncwarp();
     if (lane == 0) {
       if (warp == 0) sm.scan_tile[it % kRing] = sm.scan_tile[(it + 1) % kRing] = -1;

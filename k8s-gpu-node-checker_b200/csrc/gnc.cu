@@ -40,11 +40,12 @@ Variant make_variant(const char* name) {
 
 // Ordered by preference: the first whose stage holds an average tile with 5 % to spare is used.
 const Variant kVariants[] = {
-    make_variant<224, 2, 49664, 2>("t224"),
-    make_variant<160, 2, 49664, 2>("t160"),
-    make_variant<96, 2, 49664, 2>("t96"),
-    make_variant<64, 2, 49664, 2>("t64"),
-    make_variant<32, 2, 49664, 2>("t32"),
+    make_variant<224, 2, 48128, 2>("t224"),
+    make_variant<192, 2, 44032, 2>("t192"),
+    make_variant<128, 3, 29696, 2>("t128s3"),
+    make_variant<128, 2, 49152, 2>("t128"),
+    make_variant<64, 2, 49152, 2>("t64"),
+    make_variant<32, 2, 49152, 2>("t32"),
 };
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
@@ -138,7 +139,7 @@ int check_batch(gnc_ctx* c, const gnc_batch* in, const gnc_result* out) {
     if (!in->rows || !in->row_ptr) return fail(c, GNC_ERR_ARG, "batch.rows / batch.row_ptr is null");
     if (!aligned16(in->rows) || !aligned16(in->row_ptr))
       return fail(c, GNC_ERR_ARG, "batch.rows and batch.row_ptr must be 16-byte aligned");
-    if (in->rows_bytes > 0xFFFFFFFFull - 64) return fail(c, GNC_ERR_ARG, "rows_bytes exceeds the 4 GiB PNL-v2 limit");
+    if (in->rows_bytes > 0xFFFFFFFFull - (1u << 20)) return fail(c, GNC_ERR_ARG, "rows_bytes exceeds the PNL-v2 limit (4 GiB - 1 MiB)");
     if (!out->flags || !out->gpu_idx || !out->gpu_total || !out->gpu_vals)
       return fail(c, GNC_ERR_ARG, "result.flags / gpu_idx / gpu_total / gpu_vals is null");
     if (!aligned16(out->gpu_vals)) return fail(c, GNC_ERR_ARG, "result.gpu_vals must be 16-byte aligned");

@@ -4,13 +4,16 @@ One byte stream plus one offset column; every string the reference looks at is k
 key matching, quantity parsing and the Ready test all happen on the device, not in the packer.
 
     rows    u8[T]      node rows back to back; node i is rows[row_ptr[i] : row_ptr[i+1]]
-    row_ptr u32[N+1]   row_ptr[0] == 0 (or the shard's first byte), non-decreasing
+    row_ptr u32[N+1]   row_ptr[0] == 0 (or the shard's first byte), non-decreasing, multiples of 4
 
-    row   := cap_len:u16le [cap_len32:u32le if cap_len == 0xFFFF]
-             entry*  (exactly cap_len bytes: the node's status.capacity, in dict order)
-             entry*  (rest of the row: the node's status.conditions, as (type, status))
-    entry := klen:u8 vlen:u8 [klen32:u32le if klen == 255] [vlen32:u32le if vlen == 255]
-             key[klen] value[vlen]          (UTF-8, 'surrogatepass')
+    row  := n_cap:u8 n_cond:u8  (klen:u8 vlen:u8){n_cap + n_cond}  text  pad
+            the length table comes first so a reader steps over entries with integer adds, not
+            with one dependent load per entry; `text` is key0 value0 key1 value1 ... in table
+            order: first the node's status.capacity (dict order), then its status.conditions as
+            (type, status); `pad` is 0..3 zero bytes so that every row starts 4-byte aligned
+    xrow := 0xFF 0xFF 0 0  n_cap:u32le n_cond:u32le  (klen:u32le vlen:u32le){n_cap + n_cond}  text  pad
+            the extended form, used when a count or a length is >= 255
+    Strings are UTF-8 ('surrogatepass').
 
 Marshalling done here (type adaptation only, no classification):
   * `status` falsy or `status.capacity` falsy -> no capacity entries (check-gpu-node.py:183-185)
@@ -31,22 +34,14 @@ import numpy as np
 
 GPU_RESOURCE_KEYS = ("nvidia.com/gpu", "amd.com/gpu", "gpu.intel.com/i915", "intel.com/gpu")
 
+EMPTY_ROW = b"\0\0\0\0"
 ROWS_PAD = 32        # bytes readable past T
+MAX_ROWS_BYTES = 2 ** 32 - 2 ** 20
 ROWPTR_PAD = 4       # entries readable past N+1
 
 
 def _utf8(s: str) -> bytes:
     return s.encode("utf-8", "surrogatepass")
-
-
-def encode_entry(key: bytes, value: bytes) -> bytes:
-    kl, vl = len(key), len(value)
-    head = bytes((min(kl, 255), min(vl, 255)))
-    if kl >= 255:
-        head += struct.pack("<I", kl)
-    if vl >= 255:
-        head += struct.pack("<I", vl)
-    return head + key + value
 
 
 def marshal_quantity(value: Any) -> bytes:
@@ -62,20 +57,30 @@ def marshal_quantity(value: Any) -> bytes:
 def encode_row(capacity: Optional[Iterable[Tuple[Any, Any]]],
                conditions: Optional[Iterable[Tuple[Any, Any]]]) -> bytes:
     """One row from (key, value) pairs and (type, status) pairs."""
-    cap = bytearray()
-    for k, v in capacity or ():
-        if not isinstance(k, str):
-            continue                      # cannot equal any of the four str keys
-        cap += encode_entry(_utf8(k), marshal_quantity(v))
-    out = bytearray()
-    if len(cap) >= 0xFFFF:
-        out += b"\xff\xff" + struct.pack("<I", len(cap))
+    caps = [(_utf8(k), marshal_quantity(v)) for k, v in capacity or () if isinstance(k, str)]
+    # a non-str key cannot equal any of the four str keys: left out
+    conds = [(_utf8(t) if isinstance(t, str) else b"", _utf8(s) if isinstance(s, str) else b"")
+             for t, s in conditions or ()]
+    return encode_raw_row(caps, conds)
+
+
+def encode_raw_row(caps: Sequence[Tuple[bytes, bytes]], conds: Sequence[Tuple[bytes, bytes]],
+                   extended: Optional[bool] = None) -> bytes:
+    entries = list(caps) + list(conds)
+    if extended is None:
+        extended = len(caps) >= 255 or len(conds) >= 255 or any(len(k) >= 255 or len(v) >= 255 for k, v in entries)
+    if extended:
+        out = bytearray(b"\xff\xff\0\0") + struct.pack("<II", len(caps), len(conds))
+        for k, v in entries:
+            out += struct.pack("<II", len(k), len(v))
     else:
-        out += struct.pack("<H", len(cap))
-    out += cap
-    for t, s in conditions or ():
-        out += encode_entry(_utf8(t) if isinstance(t, str) else b"",
-                            _utf8(s) if isinstance(s, str) else b"")
+        out = bytearray((len(caps), len(conds)))
+        for k, v in entries:
+            out += bytes((len(k), len(v)))
+    for k, v in entries:
+        out += k
+        out += v
+    out += b"\0" * (-len(out) % 4)
     return bytes(out)
 
 
@@ -92,7 +97,7 @@ def node_row(node: Any, cond_cls=None) -> bytes:
     cond_cls = cond_cls or _condition_class()
     st = node.status
     if not st:
-        return b"\x00\x00"
+        return EMPTY_ROW
     cap = st.capacity.items() if st.capacity else None
     conds = None
     if st.conditions:
@@ -122,8 +127,8 @@ class PackedNodeList:
 def from_parts(rows: np.ndarray, row_ptr: np.ndarray) -> PackedNodeList:
     n = len(row_ptr) - 1
     t = int(row_ptr[n]) if n >= 0 else 0
-    if t >= 2 ** 32 - ROWS_PAD:
-        raise ValueError("PNL-v2 rows are limited to 4 GiB per list; split the fleet")
+    if t > MAX_ROWS_BYTES:
+        raise ValueError("PNL-v2 rows are limited to 4 GiB - 1 MiB per list; split the fleet")
     r = np.zeros(t + ROWS_PAD, dtype=np.uint8)
     r[:t] = rows[:t]
     p = np.full(n + 1 + ROWPTR_PAD, t, dtype=np.uint32)
@@ -147,40 +152,31 @@ def pack_nodes(nodes: Optional[Iterable[Any]]) -> PackedNodeList:
 # ---------------------------------------------------------------------------------------------
 # Reading rows back (for the host side of the bignum escape and for tests).
 # ---------------------------------------------------------------------------------------------
-def _entries(buf: bytes, pos: int, end: int) -> List[Tuple[bytes, bytes, int]]:
-    """[(key, value, value_offset)] of the entries in buf[pos:end]; stops at a malformed entry."""
-    out = []
-    while pos + 2 <= end:
-        kl, vl = buf[pos], buf[pos + 1]
-        pos += 2
-        if kl == 255:
-            if pos + 4 > end:
-                break
-            kl = struct.unpack_from("<I", buf, pos)[0]
-            pos += 4
-        if vl == 255:
-            if pos + 4 > end:
-                break
-            vl = struct.unpack_from("<I", buf, pos)[0]
-            pos += 4
-        if pos + kl + vl > end:
-            break
-        out.append((buf[pos:pos + kl], buf[pos + kl:pos + kl + vl], pos + kl))
-        pos += kl + vl
-    return out
-
-
 def decode_row(row: bytes) -> Tuple[List[Tuple[bytes, bytes]], List[Tuple[bytes, bytes]]]:
-    """(capacity entries, condition entries) of one row, as raw byte pairs."""
+    """(capacity entries, condition entries) of one row, as raw byte pairs; ([], []) if malformed."""
     if len(row) < 2:
         return [], []
-    cap_len, pos = struct.unpack_from("<H", row, 0)[0], 2
-    if cap_len == 0xFFFF:
-        if len(row) < 6:
+    if row[0] == 0xFF:
+        if len(row) < 12:
             return [], []
-        cap_len, pos = struct.unpack_from("<I", row, 2)[0], 6
-    if pos + cap_len > len(row):
-        return [], []
-    caps = [(k, v) for k, v, _ in _entries(row, pos, pos + cap_len)]
-    conds = [(k, v) for k, v, _ in _entries(row, pos + cap_len, len(row))]
-    return caps, conds
+        n_cap, n_cond = struct.unpack_from("<II", row, 4)
+        n = n_cap + n_cond
+        if 12 + 8 * n > len(row):
+            return [], []
+        lens = struct.unpack_from(f"<{2 * n}I", row, 12)
+        pos = 12 + 8 * n
+    else:
+        n_cap, n_cond = row[0], row[1]
+        n = n_cap + n_cond
+        if 2 + 2 * n > len(row):
+            return [], []
+        lens = row[2:2 + 2 * n]
+        pos = 2 + 2 * n
+    out = []
+    for i in range(n):
+        kl, vl = lens[2 * i], lens[2 * i + 1]
+        if pos + kl + vl > len(row):
+            break
+        out.append((row[pos:pos + kl], row[pos + kl:pos + kl + vl]))
+        pos += kl + vl
+    return out[:n_cap], out[n_cap:]

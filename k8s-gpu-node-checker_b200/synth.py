@@ -263,7 +263,7 @@ def expand(rows: Sequence[bytes], tid, device=None):
         row_ptr[1:n + 1] = torch.cumsum(lens[tid_t], 0)
     total = int(row_ptr[n].item()) if n else 0
     row_ptr[n + 1:] = total
-    if total >= 2 ** 32 - pnl.ROWS_PAD:
+    if total > pnl.MAX_ROWS_BYTES:
         raise ValueError("fleet exceeds the 4 GiB PNL-v2 row limit; generate it in slices")
     out = torch.zeros(total + pnl.ROWS_PAD, dtype=torch.uint8, device=dev)
     chunk = 1 << 20                                     # nodes per pass: bounds the index temporaries

@@ -131,92 +131,70 @@ static int parse_quantity(const uint8_t* s, uint32_t n, int max_digits, int64_t*
 }
 
 typedef struct {
-  uint32_t kpos, klen, vpos, vlen, next;
-} entry_t;
-
-/* Entry at pos within [pos, end). Returns 0 when it does not fit (malformed). */
-static int read_entry(const uint8_t* rows, uint64_t pos, uint64_t end, entry_t* e) {
-  if (pos + 2 > end) return 0;
-  uint64_t kl = rows[pos], vl = rows[pos + 1];
-  pos += 2;
-  if (kl == 255) {
-    if (pos + 4 > end) return 0;
-    uint32_t t;
-    memcpy(&t, rows + pos, 4);
-    kl = t;
-    pos += 4;
-  }
-  if (vl == 255) {
-    if (pos + 4 > end) return 0;
-    uint32_t t;
-    memcpy(&t, rows + pos, 4);
-    vl = t;
-    pos += 4;
-  }
-  if (pos + kl + vl > end) return 0;
-  e->kpos = (uint32_t)pos;
-  e->klen = (uint32_t)kl;
-  e->vpos = (uint32_t)(pos + kl);
-  e->vlen = (uint32_t)vl;
-  e->next = (uint32_t)(pos + kl + vl);
-  return 1;
-}
-
-typedef struct {
   uint8_t flags;
   int64_t vals[4];
   int64_t total;
   uint32_t voff[4], vlen[4];
 } node_out;
 
+static uint32_t rd32(const uint8_t* p) {
+  uint32_t t;
+  memcpy(&t, p, 4);
+  return t;
+}
+
+/* Row layout (PNL-v2, k8s-gpu-node-checker_b200/pnl.py): a length table, then the texts.
+ *   row  := n_cap:u8 n_cond:u8 (klen:u8 vlen:u8){n_cap+n_cond} text pad
+ *   xrow := 0xFF 0xFF 0 0 n_cap:u32 n_cond:u32 (klen:u32 vlen:u32){n_cap+n_cond} text pad
+ * An entry whose text would end past the row makes the row malformed and ends the walk. */
 static void classify_row(const uint8_t* rows, uint32_t s, uint32_t e, int max_digits, node_out* o) {
   int st[4] = {Q_ABSENT, Q_ABSENT, Q_ABSENT, Q_ABSENT};
   memset(o, 0, sizeof(*o));
   for (int k = 0; k < 4; k++) o->voff[k] = 0xFFFFFFFFu;
   uint32_t flags = 0;
-  uint64_t pos = s, cap_len;
   if (e - s < 2) {
-    if (e != s) flags |= F_MALFORMED;
-    o->flags = (uint8_t)flags;
+    o->flags = (e != s) ? F_MALFORMED : 0;
     return;
   }
-  cap_len = (uint64_t)rows[s] | ((uint64_t)rows[s + 1] << 8);
-  pos = s + 2;
-  if (cap_len == 0xFFFF) {
-    if (e - s < 6) { o->flags = F_MALFORMED; return; }
-    uint32_t t;
-    memcpy(&t, rows + s + 2, 4);
-    cap_len = t;
-    pos = s + 6;
+  const int ext = rows[s] == 0xFF;
+  uint64_t n_cap, n_cond, tab, stride;
+  if (ext) {
+    if (e - s < 12) { o->flags = F_MALFORMED; return; }
+    n_cap = rd32(rows + s + 4);
+    n_cond = rd32(rows + s + 8);
+    tab = (uint64_t)s + 12;
+    stride = 8;
+  } else {
+    n_cap = rows[s];
+    n_cond = rows[s + 1];
+    tab = (uint64_t)s + 2;
+    stride = 2;
   }
-  if (pos + cap_len > e) { o->flags = F_MALFORMED; return; }
-  uint64_t cap_end = pos + cap_len;
-  /* capacity: cgn.py:186-195. A repeated key overwrites (dict / json.loads last-wins). */
-  while (pos < cap_end) {
-    entry_t en;
-    if (!read_entry(rows, pos, cap_end, &en)) { flags |= F_MALFORMED; break; }
-    for (int k = 0; k < 4; k++) {
-      if (en.klen == KEY_LEN[k] && memcmp(rows + en.kpos, KEYS[k], KEY_LEN[k]) == 0) {
-        int64_t v = 0;
-        st[k] = parse_quantity(rows + en.vpos, en.vlen, max_digits, &v);
-        o->vals[k] = st[k] == Q_OK ? v : 0;
-        o->voff[k] = st[k] == Q_ABSENT ? 0xFFFFFFFFu : en.vpos;
-        o->vlen[k] = st[k] == Q_ABSENT ? 0 : en.vlen;
+  const uint64_t n = n_cap + n_cond;
+  uint64_t off = tab + stride * n;
+  if (off > e) { o->flags = F_MALFORMED; return; }
+  for (uint64_t i = 0; i < n; i++) {
+    const uint64_t kl = ext ? rd32(rows + tab + 8 * i) : rows[tab + 2 * i];
+    const uint64_t vl = ext ? rd32(rows + tab + 8 * i + 4) : rows[tab + 2 * i + 1];
+    if (off + kl + vl > e) { flags |= F_MALFORMED; break; }
+    const uint8_t* key = rows + off;
+    const uint8_t* val = rows + off + kl;
+    if (i < n_cap) {
+      /* capacity: cgn.py:186-195. A repeated key overwrites (dict / json.loads last-wins). */
+      for (int k = 0; k < 4; k++) {
+        if (kl == KEY_LEN[k] && memcmp(key, KEYS[k], KEY_LEN[k]) == 0) {
+          int64_t v = 0;
+          st[k] = parse_quantity(val, (uint32_t)vl, max_digits, &v);
+          o->vals[k] = st[k] == Q_OK ? v : 0;
+          o->voff[k] = st[k] == Q_ABSENT ? 0xFFFFFFFFu : (uint32_t)(off + kl);
+          o->vlen[k] = st[k] == Q_ABSENT ? 0 : (uint32_t)vl;
+        }
       }
-    }
-    pos = en.next;
-  }
-  /* conditions: cgn.py:175-177 */
-  pos = cap_end;
-  while (pos < e) {
-    entry_t en;
-    if (!read_entry(rows, pos, e, &en)) { flags |= F_MALFORMED; break; }
-    if (en.klen == 5 && en.vlen == 4 && memcmp(rows + en.kpos, "Ready", 5) == 0 &&
-        memcmp(rows + en.vpos, "True", 4) == 0) {
-      flags |= F_READY;
+    } else if (kl == 5 && vl == 4 && memcmp(key, "Ready", 5) == 0 && memcmp(val, "True", 4) == 0) {
+      flags |= F_READY; /* conditions: cgn.py:175-177, first hit returns */
       break;
     }
-    pos = en.next;
+    off += kl + vl;
   }
   int big = 0;
   int64_t total = 0;

@@ -147,7 +147,7 @@ def test_1m_adversarial_fleet(clf, g2):
     assert fr.exit_code == 0
 
 
-@pytest.mark.parametrize("variant", ["t224", "t160", "t96", "t64", "t32"])
+@pytest.mark.parametrize("variant", ["t224", "t192", "t128s3", "t128", "t64", "t32"])
 def test_every_kernel_variant(g2, variant, monkeypatch):
     """Each tile shape, on a fleet with rows too large to stage (read straight from global memory)."""
     tmpl, rows, truth, _ = g2
@@ -180,9 +180,8 @@ def test_host_buffer_entry_point(clf, g2):
 
 
 def test_malformed_rows_match_oracle(clf):
-    good = pnl.encode_row([("nvidia.com/gpu", "4")], [("Ready", "True")])
-    bad = [good[:1], good[:5], b"\xff\xff\x01", b"\x40\x00" + good[2:10], good[:2] + b"\x0e\x09nvidia.com/gpu4",
-           good[:-3], b"\x02\x00\xff\x01", b""]
+    from tests.test_oracle_pnl import bad_rows
+    good, bad = bad_rows()
     rows = []
     for b in bad:
         rows += [good, b] * 40
@@ -190,13 +189,26 @@ def test_malformed_rows_match_oracle(clf):
     got = run_device(clf, p)
     ora = po.classify(p.rows, p.row_ptr, p.n_nodes)
     assert_same_outputs(got, ora, "malformed")
-    assert int(got["counts"][12]) == 40 * (len(bad) - 1)
+    assert int(got["counts"][12]) == 40 * len(bad)
     # a row_ptr that runs backwards or past the data is contained, not followed
     rp = p.row_ptr.copy()
     rp[5], rp[9] = rp[7], 0xFFFFFF00
     q = pnl.PackedNodeList(p.rows, rp, p.n_nodes)
     got = run_device(clf, q)
-    assert int(got["counts"][12]) >= 40 * (len(bad) - 1)
+    assert int(got["counts"][12]) >= 40 * len(bad)
+
+
+def test_extended_and_misaligned_rows(clf):
+    """32-bit-length rows and rows that do not start on a 4-byte boundary take the general walk."""
+    caps = [(b"cpu", b"4"), (b"amd.com/gpu", b" 2 "), (b"nvidia.com/gpu", b"7")]
+    conds = [(b"DiskPressure", b"False"), (b"Ready", b"True")]
+    rows = [pnl.encode_raw_row(caps, conds, extended=False), pnl.encode_raw_row(caps, conds, extended=True),
+            pnl.encode_raw_row(caps, conds, extended=False)[:-1], pnl.encode_raw_row(caps[:2], conds[:1], extended=False)] * 100
+    p = pnl.from_rows(rows)
+    got = run_device(clf, p)
+    ora = po.classify(p.rows, p.row_ptr, p.n_nodes)
+    assert_same_outputs(got, ora, "extended/misaligned")
+    assert int(got["counts"][0]) == 400 and int(got["counts"][1]) == 300 and int(got["counts"][12]) == 0
 
 
 def test_output_capacity_is_respected(clf, g2):

@@ -103,11 +103,25 @@ def test_pack_unpack_roundtrip(g2):
         assert conds == [(a.encode(), b.encode()) for a, b in wc]
 
 
-def test_malformed_rows_are_contained():
-    """Truncated / lying lengths never read outside the row; the row is flagged and classifies as empty."""
+def bad_rows():
+    """Rows whose own lengths do not fit them (each 4-byte padded, as the format requires)."""
     good = pnl.encode_row([("nvidia.com/gpu", "4")], [("Ready", "True")])
-    bad = [good[:1], good[:5], b"\xff\xff\x01", b"\x40\x00" + good[2:10], good[:2] + b"\x0e\x09nvidia.com/gpu4",
-           good[:-3], b"\x02\x00\xff\x01"]
+    pad = lambda b: b + b"\0" * (-len(b) % 4)   # noqa: E731
+    return good, [
+        b"\x01",                                         # one byte: no header
+        pad(b"\x05\x05\x01\x01"),                        # table longer than the row
+        pad(b"\x01\x00\x0e\x09nvidia.com/gpu4"),          # value length overruns the row
+        pad(b"\x01\x01\x0e\x01\x05\x09nvidia.com/gpu4ReadyTrue"),   # condition overruns; capacity before it counts
+        pad(b"\xff\xff\0\0\x01\0\0"),                   # extended header cut short
+        pad(b"\xff\xff\0\0" + b"\xff\xff\xff\x7f" * 2),   # extended counts far beyond the row
+        pad(b"\xff\xff\0\0\x01\0\0\0\0\0\0\0\xff\xff\xff\xff\x01\0\0\0k"),   # 4 GiB key length
+        good[:-8],                                       # text cut short
+    ]
+
+
+def test_malformed_rows_are_contained():
+    """Truncated / lying lengths never read outside the row; the row is flagged, earlier entries count."""
+    good, bad = bad_rows()
     rows = []
     for b in bad:
         rows += [good, b]
@@ -117,7 +131,22 @@ def test_malformed_rows_are_contained():
     assert all(f[i] & F_GPU for i in range(0, len(f), 2))
     assert all(f[i] & F_MALFORMED for i in range(1, len(f), 2))
     assert int(got["counts"][12]) == len(bad)
-    assert int(got["counts"][0]) == len(bad) + 1 + sum(1 for i in range(1, len(f), 2) if f[i] & F_GPU)
+    assert f[2 * 3 + 1] & F_GPU and not f[2 * 3 + 1] & 2     # capacity entry kept, overrunning Ready not seen
+    assert f[2 * 7 + 1] & F_GPU and not f[2 * 7 + 1] & 2     # likewise when the text is cut short
+    assert int(got["counts"][0]) == len(bad) + 1 + 2
+
+
+def test_extended_rows_equal_short_rows():
+    """The 32-bit-length form classifies exactly like the 8-bit form of the same entries."""
+    caps = [(b"cpu", b"4"), (b"amd.com/gpu", b" 2 "), (b"nvidia.com/gpu", b"1" * 23)]
+    conds = [(b"DiskPressure", b"False"), (b"Ready", b"True")]
+    a = pnl.from_rows([pnl.encode_raw_row(caps, conds, extended=False), pnl.encode_raw_row(caps[:2], conds, extended=False)])
+    b = pnl.from_rows([pnl.encode_raw_row(caps, conds, extended=True), pnl.encode_raw_row(caps[:2], conds, extended=True)])
+    ra, rb = po.classify(a.rows, a.row_ptr, 2), po.classify(b.rows, b.row_ptr, 2)
+    np.testing.assert_array_equal(ra["flags"], rb["flags"])
+    np.testing.assert_array_equal(ra["gpu_vals"], rb["gpu_vals"])
+    assert ra["flags"][0] & F_DEFERRED and ra["flags"][1] & F_GPU
+    assert pnl.decode_row(b.row(0)) == (caps, conds)
 
 
 _chars = st.sampled_from(list("0123456789_+- \t\n\x0b\x0c\r\x1c\x00kKi.e") +
