@@ -120,7 +120,7 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity
         : "r"(addr), "r"(parity)
         : "memory");
     if (ok) break;
-    __nanosleep(64);
+    __nanosleep(200);
   }
 }
 // global -> shared bulk copy; src, dst and bytes are multiples of 16.
@@ -437,9 +437,9 @@ __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_
     return true;
   }
   if ((s & 3u) || e - s >= 65536u) return false;
-  const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + s);
-  uint32_t w = wp[0];
-  const uint32_t n_cap = w & 0xFFu, n_cond = (w >> 8) & 0xFFu;
+  const uint16_t* tab = reinterpret_cast<const uint16_t*>(buf + s);  // tab[0] header, tab[1 + i] = (klen, vlen) of entry i
+  const uint32_t hdr = tab[0];
+  const uint32_t n_cap = hdr & 0xFFu, n_cond = hdr >> 8;
   if (n_cap == 0xFFu) return false;
   const uint32_t n = n_cap + n_cond;
   uint32_t rel = 2u + 2u * n;  // row-relative offset of the text of the next entry
@@ -449,29 +449,25 @@ __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_
   }
   uint32_t k0 = 0, k1 = 0, k2 = 0, k3 = 0, nk = 0;  // capacity candidates, k0 newest
   uint32_t q0 = 0, q1 = 0, nq = 0;                  // condition candidates, q0 newest
-  uint32_t ff = __vcmpeq4(w | 0x0000FFFFu, 0xFFFFFFFFu) & 0xFFFF0000u;  // a 0xFF length byte anywhere
-  auto step = [&](uint32_t hv, uint32_t idx) {
-    const uint32_t kl = hv & 0xFFu, len = kl + (hv >> 8);
-    const bool valid = idx < n, in_cap = idx < n_cap;
-    const bool ccap = valid && in_cap && ((0x46800u >> kl) & 1u) && kl < 32u;
-    const bool ccond = valid && !in_cap && hv == (5u | (4u << 8));
-    const uint32_t rec = (rel << 16) | hv;
-    if (ccap) {
-      k3 = k2, k2 = k1, k1 = k0, k0 = rec;
+  uint32_t ff = 0;                                  // a 0xFF length byte anywhere in the table
+  uint32_t idx = 0;
+  for (; idx < n_cap; ++idx) {
+    const uint32_t hv = tab[1 + idx], kl = hv & 0xFFu;
+    ff |= __vcmpeq4(hv, 0xFFFFFFFFu);
+    if (((0x46800u >> (kl & 31u)) & 1u) && kl < 32u) {
+      k3 = k2, k2 = k1, k1 = k0, k0 = (rel << 16) | hv;
       ++nk;
     }
-    if (ccond) {
-      q1 = q0, q0 = rec;
+    rel += kl + (hv >> 8);
+  }
+  for (; idx < n; ++idx) {
+    const uint32_t hv = tab[1 + idx];
+    ff |= __vcmpeq4(hv, 0xFFFFFFFFu);
+    if (hv == (5u | (4u << 8))) {
+      q1 = q0, q0 = (rel << 16) | hv;
       ++nq;
     }
-    rel += valid ? len : 0u;
-  };
-  step(w >> 16, 0);
-  for (uint32_t j = 1; 2 * j - 1 < n; ++j) {
-    w = wp[j];
-    ff |= __vcmpeq4(w, 0xFFFFFFFFu);
-    step(w & 0xFFFFu, 2 * j - 1);
-    step(w >> 16, 2 * j);
+    rel += (hv & 0xFFu) + (hv >> 8);
   }
   if (ff || nk > 4u || nq > 2u || rel >= 65536u) return false;
   const uint32_t row_len = e - s;
