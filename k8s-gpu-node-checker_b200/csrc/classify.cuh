@@ -123,6 +123,19 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity
     __nanosleep(200);
   }
 }
+// for warps with nothing else to do: let the hardware park the thread for up to ~1 us per try
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+  uint32_t addr = smem_addr(bar), ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity), "r"(1000u)
+        : "memory");
+  } while (!ok);
+}
 // global -> shared bulk copy; src, dst and bytes are multiples of 16.
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -427,8 +440,8 @@ __device__ __forceinline__ void resolve_key(const uint8_t* buf, uint32_t s, uint
 //     condition of lengths 5 and 4) are pushed into small shift registers;
 //  2. look at the candidates' text, oldest first.  Every lane has about the same number of
 //     candidates, so the warp stays converged here whatever position the keys had in the rows.
-// Returns false when the row needs the general walk (extended form, a 0xFF byte in the table,
-// misaligned or >= 64 KB row, more candidates than the registers hold).
+// Returns false when the row needs the general walk (extended form, misaligned or >= 64 KB row,
+// more candidates than the registers hold).
 __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, NodeResult& r) {
   r.v01 = r.v23 = 0;
   r.bits = 0;
@@ -449,11 +462,9 @@ __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_
   }
   uint32_t k0 = 0, k1 = 0, k2 = 0, k3 = 0, nk = 0;  // capacity candidates, k0 newest
   uint32_t q0 = 0, q1 = 0, nq = 0;                  // condition candidates, q0 newest
-  uint32_t ff = 0;                                  // a 0xFF length byte anywhere in the table
   uint32_t idx = 0;
   for (; idx < n_cap; ++idx) {
     const uint32_t hv = tab[1 + idx], kl = hv & 0xFFu;
-    ff |= __vcmpeq4(hv, 0xFFFFFFFFu);
     if (((0x46800u >> (kl & 31u)) & 1u) && kl < 32u) {
       k3 = k2, k2 = k1, k1 = k0, k0 = (rel << 16) | hv;
       ++nk;
@@ -462,17 +473,19 @@ __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_
   }
   for (; idx < n; ++idx) {
     const uint32_t hv = tab[1 + idx];
-    ff |= __vcmpeq4(hv, 0xFFFFFFFFu);
     if (hv == (5u | (4u << 8))) {
       q1 = q0, q0 = (rel << 16) | hv;
       ++nq;
     }
     rel += (hv & 0xFFu) + (hv >> 8);
   }
-  if (ff || nk > 4u || nq > 2u || rel >= 65536u) return false;
+  if (nk > 4u || nq > 2u || rel >= 65536u) return false;
   const uint32_t row_len = e - s;
   bool stop = false;
-  // capacity candidates, oldest first: bounds, then the first four key bytes
+  // capacity candidates, oldest first: bounds, then the first four key bytes.  The few that pass
+  // (one per GPU node) are resolved afterwards, so that lanes whose key sat at different candidate
+  // positions compare key tails and parse values together.
+  uint32_t real_a = 0, real_b = 0, n_real = 0;  // real_a older
 #pragma unroll
   for (int i = 3; i >= 0; --i) {
     const uint32_t rec = i == 3 ? k3 : i == 2 ? k2 : i == 1 ? k1 : k0;
@@ -483,10 +496,17 @@ __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_
         stop = true;
       } else {
         const uint32_t e0 = kl == 14u ? pack4("nvid", 0, 4) : kl == 11u ? pack4("amd.", 0, 4) : kl == 18u ? pack4("gpu.", 0, 4) : pack4("inte", 0, 4);
-        if (ld32u(buf, s + (rec >> 16)) == e0) resolve_key(buf, s, rec, max_digits, r);
+        if (ld32u(buf, s + (rec >> 16)) == e0) {
+          real_a = real_b;
+          real_b = rec;
+          ++n_real;
+        }
       }
     }
   }
+  if (n_real > 2u) return false;
+  if (n_real > 1u) resolve_key(buf, s, real_a, max_digits, r);
+  if (n_real > 0u) resolve_key(buf, s, real_b, max_digits, r);
   // condition candidates, oldest first: the first (Ready, True) ends the walk (check-gpu-node.py:176-177)
 #pragma unroll
   for (int i = 1; i >= 0; --i) {
@@ -589,7 +609,7 @@ struct Smem {
   uint32_t lo[STAGES];
   uint32_t hi[STAGES];      // rows of the tile must end at or before this byte
   uint32_t direct[STAGES];  // 1: tile too large to stage, rows are read from global memory
-  int part[kRing][TN / 32][P_N];
+  alignas(16) int part[kRing][TN / 32][P_N];
   uint32_t warp_base[kRing][TN / 32];
   int scan_tile[kRing];
   uint32_t tile_cnt[kRing];  // [31:16] walker warps done with the tile, [15:0] GPU nodes counted so far
@@ -633,7 +653,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         const uint32_t ph = (it / STAGES) & 1u;
         const uint32_t tile = atomicAdd(&p.scratch->ticket, 1u);
         if (tile >= p.num_tiles) {
-          mbar_wait_backoff(&sm.empty[s], ph ^ 1u);
+          mbar_wait_parked(&sm.empty[s], ph ^ 1u);
           sm.tile[s] = -1;
           mbar_arrive(&sm.full[s]);
           break;
@@ -645,7 +665,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         const uint32_t bytes = ((hi + 15u) & ~15u) - lo_al;
         const uint32_t rp_bytes = ((cnt + 1) * 4u + 15u) & ~15u;
         const bool direct = hi < lo || hi > p.rows_bytes || bytes > (uint32_t)STAGE_BYTES;
-        mbar_wait_backoff(&sm.empty[s], ph ^ 1u);
+        mbar_wait_parked(&sm.empty[s], ph ^ 1u);
         sm.tile[s] = (int)tile;
         sm.lo[s] = lo_al;
         sm.hi[s] = direct ? (uint32_t)min(p.rows_bytes, (uint64_t)0xFFFFFFFFu) : hi;
@@ -662,7 +682,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
     long long a_gpu = 0, a_ready = 0, a_def = 0, a_bad = 0, a_key[4] = {0, 0, 0, 0};  // lane 0 only
     for (uint32_t it = warp - kWalkWarps - 1;; it += 2) {
       const int b = it % kRing;
-      mbar_wait_backoff(&sm.cnt_full[b], (it / kRing) & 1u);
+      mbar_wait_parked(&sm.cnt_full[b], (it / kRing) & 1u);
       const int tile = sm.scan_tile[b];
       if (tile < 0) break;
       GNC_T(5, it, gtimer());
@@ -802,15 +822,9 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       const int s3 = __reduce_add_sync(0xFFFFFFFFu, count_narrow ? v3 : 0);
       const int b = it % kRing;
       if (lane == 0) {
-        int* pp = sm.part[b][warp];
-        pp[P_GPU] = __popc(gb);
-        pp[P_READY] = n_ready;
-        pp[P_DEFERRED] = n_def;
-        pp[P_MALFORMED] = n_bad;
-        pp[P_KEY0 + 0] = s0;
-        pp[P_KEY0 + 1] = s1;
-        pp[P_KEY0 + 2] = s2;
-        pp[P_KEY0 + 3] = s3;
+        int4* pp = reinterpret_cast<int4*>(sm.part[b][warp]);
+        pp[0] = make_int4(__popc(gb), (int)n_ready, (int)n_def, (int)n_bad);  // P_GPU, P_READY, P_DEFERRED, P_MALFORMED
+        pp[1] = make_int4(s0, s1, s2, s3);                                     // P_KEY0 ..
         if (warp == 0) sm.scan_tile[b] = tile;
         // the last warp to count its share publishes the tile's aggregate at once: other CTAs'
         // look-backs must never wait for this CTA's scan warp to get round to the tile
