@@ -40,7 +40,7 @@ Variant make_variant(const char* name) {
 
 // Ordered by preference: the first whose stage holds an average tile with 5 % to spare is used.
 const Variant kVariants[] = {
-    make_variant<224, 2, 48128, 2>("t224"),
+    make_variant<224, 2, 49792, 2>("t224"),
     make_variant<192, 2, 44032, 2>("t192"),
     make_variant<128, 3, 29696, 2>("t128s3"),
     make_variant<128, 2, 49152, 2>("t128"),
