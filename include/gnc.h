@@ -122,6 +122,27 @@ int gnc_gather(gnc_ctx*, const gnc_result* local, const gnc_result* all, void* c
  * host memory.  This is the call a binding without device buffers of its own uses. */
 int gnc_classify_host(gnc_ctx*, const gnc_batch* host_in, const gnc_result* host_out);
 
+/* The same classification as gnc_classify for callers that cannot allocate: no context, no
+ * cudaMalloc or cudaFree, no allocating library call, on any call.  (No counterpart in the
+ * reference; it exists for hosts that run under a device-memory cap they have already spent, or that
+ * cannot take the device-wide synchronisation and possible failure of an allocation on their path.)
+ * The kernel's scratch is a fixed array inside libgnc.so, GNC_STATIC_SCRATCH_BYTES of device memory
+ * that every GPU which loads the library holds until the process exits.  It serves shards of up to
+ * GNC_STATIC_MAX_TILES tiles -- about 14.6M nodes of ordinary size (224 per tile), fewer when rows
+ * are large (down to 32 per tile, 2M nodes); a larger shard is refused with GNC_ERR_ARG and a text
+ * saying so.  Inputs and outputs are the caller's DEVICE buffers, exactly as for gnc_classify;
+ * max_str_digits is sys.get_int_max_str_digits() (4300 by default, 0 = no limit).
+ *  - The first call on each device looks up the array's device address and the launch geometry.
+ *    Make that call outside any stream capture.
+ *  - All calls on a device share the one array, which keeps the previous call's contents; each call
+ *    clears what has to start from zero, on `cuda_stream`.  Two calls whose kernels overlap on the
+ *    GPU (different streams, different threads) race on it: order them.
+ * `err` (may be NULL) receives the error text, at most err_cap bytes. */
+#define GNC_STATIC_MAX_TILES 65536
+#define GNC_STATIC_SCRATCH_BYTES (256 + GNC_STATIC_MAX_TILES * 12)
+int gnc_classify_static(int device, const gnc_batch* in, const gnc_result* out, int max_str_digits,
+                        void* cuda_stream, char* err, size_t err_cap);
+
 /* Kernels this context has launched since it was created (for benchmark accounting). */
 uint64_t gnc_launch_count(const gnc_ctx*);
 

@@ -592,3 +592,134 @@ extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result*
   c->launches += 2;
   return GNC_OK;
 }
+
+
+// =================================================================================================
+// Classification without any allocation (gnc_classify_static, include/gnc.h).
+//
+// Some hosts of this library may not allocate device memory at all once they are running: an agent
+// admitted to a node under a hard device-memory cap that is already spent on its buffers, or a
+// caller on a latency path that cannot afford cudaMalloc's device-wide synchronisation (or its
+// failure).  For them the kernel's scratch -- the tile ticket, the accumulators and the look-back
+// descriptors that gnc_create otherwise cudaMallocs -- lives in the file-scope array below, which
+// every GPU that loads libgnc.so carries from module load until the process exits.
+// =================================================================================================
+namespace {
+
+constexpr size_t kStaticScratchBytes = sizeof(ScratchHeader) + (size_t)GNC_STATIC_MAX_TILES * (sizeof(unsigned long long) + sizeof(uint32_t));
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// Per-device host-side state for the static path.  `scratch` is the DEVICE address of
+// g_static_scratch on that device: in host code the array's name is only a handle for the runtime,
+// not an address a kernel could use, so the address is asked for once per device.
+constexpr int kStaticMaxDevices = 64;
+struct StaticState {
+  bool ready;
+  void* scratch;
+  uint32_t epoch;
+  int sm_count;
+  int ctas_per_sm[kNumVariants];
+};
+StaticState g_static_state[kStaticMaxDevices];
+
+int static_fail(char* err, size_t cap, int code, const char* what, const char* detail) {
+  if (err && cap) snprintf(err, cap, "%s%s%s", what, detail ? ": " : "", detail ? detail : "");
+  return code;
+}
+#define STATIC_CUDA_TRY(expr)                                                              \
+  do {                                                                                     \
+    cudaError_t e_ = (expr);                                                               \
+    if (e_ != cudaSuccess) return static_fail(err, err_cap, GNC_ERR_CUDA, #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+}  // namespace
+
+extern "C" int gnc_classify_static(int device, const gnc_batch* in, const gnc_result* out, int max_str_digits,
+                                   void* cuda_stream, char* err, size_t err_cap) {
+  if (err && err_cap) err[0] = 0;
+  if (device < 0 || device >= kStaticMaxDevices) return static_fail(err, err_cap, GNC_ERR_ARG, "device index outside [0, 64)", nullptr);
+  if (!in || !out || !out->counts) return static_fail(err, err_cap, GNC_ERR_ARG, "null batch, result or counts", nullptr);
+  if (max_str_digits < 0) return static_fail(err, err_cap, GNC_ERR_ARG, "max_str_digits is negative", nullptr);
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  STATIC_CUDA_TRY(cudaSetDevice(device));
+  StaticState& st = g_static_state[device];
+  if (!st.ready) {
+    // First call on this device (it is current): learn the device address of the scratch array and
+    // the launch geometry.  Nothing here allocates; it must not run inside a stream capture.
+    void* ptr = nullptr;
+    STATIC_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    cudaDeviceProp prop;
+    STATIC_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return static_fail(err, err_cap, GNC_ERR_STATE, "libgnc is built for sm_100a (B200); device is", prop.name);
+    for (int v = 0; v < kNumVariants; v++) {
+      STATIC_CUDA_TRY(cudaFuncSetAttribute(kVariants[v].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVariants[v].smem));
+      int n = 0;
+      STATIC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kVariants[v].fn, kVariants[v].threads, kVariants[v].smem));
+      if (n < 1) return static_fail(err, err_cap, GNC_ERR_STATE, "kernel variant does not fit an SM", kVariants[v].name);
+      st.ctas_per_sm[v] = n;
+    }
+    st.sm_count = prop.multiProcessorCount;
+    st.scratch = ptr;
+    st.epoch = 0;
+    st.ready = true;
+  }
+  if (in->n_nodes == 0) {
+    STATIC_CUDA_TRY(cudaMemsetAsync(out->counts, 0, GNC_N_COUNTS * sizeof(int64_t), stream));
+    return GNC_OK;
+  }
+  if (!in->rows || !in->row_ptr || !out->flags || !out->gpu_idx || !out->gpu_total || !out->gpu_vals)
+    return static_fail(err, err_cap, GNC_ERR_ARG, "null input or output buffer", nullptr);
+  if (!aligned16(in->rows) || !aligned16(in->row_ptr) || !aligned16(out->gpu_vals))
+    return static_fail(err, err_cap, GNC_ERR_ARG, "rows, row_ptr and gpu_vals must be 16-byte aligned", nullptr);
+  if (in->rows_bytes > 0xFFFFFFFFull - (1u << 20)) return static_fail(err, err_cap, GNC_ERR_ARG, "rows_bytes exceeds the PNL-v2 limit (4 GiB - 1 MiB)", nullptr);
+  if ((uint64_t)in->node_base + in->n_nodes > 0x100000000ull) return static_fail(err, err_cap, GNC_ERR_ARG, "node_base + n_nodes exceeds 2^32", nullptr);
+  if (out->defer_cap && !out->defer) return static_fail(err, err_cap, GNC_ERR_ARG, "result.defer is null but defer_cap > 0", nullptr);
+
+  // same tile-shape choice as gnc_classify
+  int v = kNumVariants - 1;
+  const double avg = (double)in->rows_bytes / in->n_nodes;
+  for (int q = 0; q < kNumVariants; q++)
+    if (avg * kVariants[q].tile_nodes * 1.05 + 32 <= kVariants[q].stage_bytes) { v = q; break; }
+  const Variant& var = kVariants[v];
+  const uint32_t tiles = tiles_for(in->n_nodes, var.tile_nodes);
+  if (tiles > GNC_STATIC_MAX_TILES) {
+    char msg[160];
+    snprintf(msg, sizeof msg, "%u nodes at %d nodes per tile need %u tiles; the static scratch holds %d (use gnc_classify, or split the shard)",
+             in->n_nodes, var.tile_nodes, tiles, GNC_STATIC_MAX_TILES);
+    return static_fail(err, err_cap, GNC_ERR_ARG, "shard too large for gnc_classify_static", msg);
+  }
+  // The array still holds whatever the previous call left.  The header (ticket, finished-CTA count,
+  // accumulators) must start at zero; the descriptors are told apart by the epoch tag instead, and
+  // are wiped only when the 22-bit epoch wraps.
+  STATIC_CUDA_TRY(cudaMemsetAsync(st.scratch, 0, sizeof(ScratchHeader), stream));
+  st.epoch = (st.epoch + 1) & gnc::kEpochMask;
+  if (st.epoch == 0) {
+    STATIC_CUDA_TRY(cudaMemsetAsync((char*)st.scratch + sizeof(ScratchHeader), 0, kStaticScratchBytes - sizeof(ScratchHeader), stream));
+    st.epoch = 1;
+  }
+  Params p;
+  p.rows = in->rows;
+  p.row_ptr = in->row_ptr;
+  p.rows_bytes = in->rows_bytes;
+  p.n_nodes = in->n_nodes;
+  p.node_base = in->node_base;
+  p.num_tiles = tiles;
+  p.epoch = st.epoch;
+  p.max_digits = max_str_digits;
+  p.flags = out->flags;
+  p.gpu_idx = out->gpu_idx;
+  p.gpu_total = out->gpu_total;
+  p.gpu_vals = out->gpu_vals;
+  p.defer = out->defer;
+  p.counts = out->counts;
+  p.out_cap = out->out_cap;
+  p.defer_cap = out->defer ? out->defer_cap : 0;
+  p.scratch = (ScratchHeader*)st.scratch;
+  p.inc = (unsigned long long*)((char*)st.scratch + sizeof(ScratchHeader));
+  p.agg = (uint32_t*)(p.inc + GNC_STATIC_MAX_TILES);
+  p.trace = nullptr;
+  const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(st.sm_count * st.ctas_per_sm[v]));
+  var.launch(p, grid, var.smem, stream);
+  STATIC_CUDA_TRY(cudaGetLastError());
+  return GNC_OK;
+}

@@ -10,6 +10,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libgnc.so")
 ABI_VERSION = 2
 N_COUNTS = 16
+STATIC_MAX_TILES = 65536
 
 F_GPU, F_READY, F_DEFERRED, F_KEY0, F_MALFORMED = 0x01, 0x02, 0x04, 0x08, 0x80
 C_GPU_NODES, C_READY_NODES, C_DEFERRED, C_SCANNED, C_KEY_LO, C_KEY_HI = 0, 1, 2, 3, 4, 8
@@ -32,7 +33,7 @@ class Result(ctypes.Structure):
 
 
 EXPORTS = ("gnc_abi_version", "gnc_create", "gnc_comm_id", "gnc_reserve", "gnc_set_max_str_digits", "gnc_classify",
-           "gnc_gather", "gnc_classify_host", "gnc_launch_count", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
+           "gnc_gather", "gnc_classify_host", "gnc_classify_static", "gnc_launch_count", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
 
 
 class GncError(RuntimeError):
@@ -71,6 +72,9 @@ def lib() -> ctypes.CDLL:
     L.gnc_classify.argtypes = [vp, ctypes.POINTER(Batch), ctypes.POINTER(Result), vp]
     L.gnc_gather.argtypes = [vp, ctypes.POINTER(Result), ctypes.POINTER(Result), vp]
     L.gnc_classify_host.argtypes = [vp, ctypes.POINTER(Batch), ctypes.POINTER(Result)]
+    L.gnc_classify_static.argtypes = [i32, ctypes.POINTER(Batch), ctypes.POINTER(Result), i32, vp, ctypes.c_char_p,
+                                      ctypes.c_size_t]
+    L.gnc_classify_static.restype = i32
     L.gnc_launch_count.argtypes = [vp]
     L.gnc_launch_count.restype = ctypes.c_uint64
     L.gnc_unicode_tables.argtypes = [ctypes.POINTER(ctypes.POINTER(u32)), ctypes.POINTER(i32),
