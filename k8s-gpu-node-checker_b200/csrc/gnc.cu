@@ -84,6 +84,8 @@ struct gnc_ctx {
   void* comm = nullptr;
   int64_t* d_all_counts = nullptr;  // [world][GNC_N_COUNTS]
   int64_t* h_all_counts = nullptr;  // pinned
+  uint32_t* gather_buf = nullptr;   // [world][32 + gather_cap] u32: counts block + indices of every rank
+  size_t gather_cap = 0;
   std::string err;
 };
 
@@ -527,7 +529,61 @@ void comm_destroy(gnc_ctx* c) {
   if (c->comm) nccl_api()->CommDestroy(c->comm);
   c->comm = nullptr;
   cudaFree(c->d_all_counts);
+  cudaFree(c->gather_buf);
   if (c->h_all_counts) cudaFreeHost(c->h_all_counts);
+}
+
+}  // namespace
+
+namespace {
+
+// One rank's slot of the gather buffer, in u32 units: [0, 32) its counts block, [32, 32 + cap) its indices.
+constexpr uint32_t kSlotHeader = 2 * GNC_N_COUNTS;
+
+__global__ void gather_pack_kernel(const int64_t* counts, const uint32_t* idx, uint32_t* slot, uint32_t cap) {
+  const unsigned long long g = min((unsigned long long)counts[GNC_C_GPU_NODES], (unsigned long long)cap);
+  if (blockIdx.x == 0 && threadIdx.x < kSlotHeader) slot[threadIdx.x] = reinterpret_cast<const uint32_t*>(counts)[threadIdx.x];
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < g; i += (unsigned long long)gridDim.x * blockDim.x)
+    slot[kSlotHeader + i] = idx[i];
+}
+
+// Every rank's slot -> one dense, rank-ordered index list and the exact sum of the counts blocks.
+__global__ void gather_unpack_kernel(const uint32_t* buf, uint32_t slot_u32, uint32_t cap, int world, uint32_t* out_idx,
+                                     uint32_t out_cap, int64_t* out_counts) {
+  __shared__ unsigned long long off[65];
+  if (threadIdx.x == 0) {
+    off[0] = 0;
+    for (int r = 0; r < world; r++) off[r + 1] = off[r] + (unsigned long long)reinterpret_cast<const int64_t*>(buf + (size_t)r * slot_u32)[GNC_C_GPU_NODES];
+  }
+  __syncthreads();
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x, t0 = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  for (int r = 0; r < world; r++) {
+    const uint32_t* src = buf + (size_t)r * slot_u32 + kSlotHeader;
+    const unsigned long long cnt = min(off[r + 1] - off[r], (unsigned long long)cap);
+    for (unsigned long long i = t0; i < cnt; i += stride)
+      if (off[r] + i < out_cap) out_idx[off[r] + i] = src[i];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    long long sum[GNC_N_COUNTS];
+    unsigned __int128 key[4] = {0, 0, 0, 0};
+    unsigned long long lost = 0;
+    for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] = 0;
+    for (int r = 0; r < world; r++) {
+      const long long* cr = reinterpret_cast<const long long*>(buf + (size_t)r * slot_u32);
+      for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] += cr[s];
+      for (int k = 0; k < 4; k++)
+        key[k] += ((unsigned __int128)(unsigned long long)cr[GNC_C_KEY_HI + k] << 64) | (unsigned long long)cr[GNC_C_KEY_LO + k];
+      const unsigned long long cnt = off[r + 1] - off[r];
+      if (cnt > cap) lost += cnt - cap;
+    }
+    if (off[world] > out_cap) lost = max(lost, off[world] - out_cap);
+    for (int k = 0; k < 4; k++) {
+      sum[GNC_C_KEY_LO + k] = (long long)(unsigned long long)key[k];
+      sum[GNC_C_KEY_HI + k] = (long long)(unsigned long long)(key[k] >> 64);
+    }
+    sum[GNC_C_OUT_DROPPED] += (long long)lost;
+    for (int s = 0; s < GNC_N_COUNTS; s++) out_counts[s] = sum[s];
+  }
 }
 
 }  // namespace
@@ -554,6 +610,34 @@ extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result*
   }
   if (!c->comm) return fail(c, GNC_ERR_STATE, "context has no communicator");
   NcclApi* n = nccl_api();
+  if (!all->gpu_total && !all->gpu_vals) {
+    // Indices and counts only (the north star's gather): ONE in-place all-gather of fixed-size slots
+    // -- each rank's counts block followed by its indices -- then a kernel that packs the slots into
+    // the dense rank-ordered list and adds the counts up.  No host round trip, nothing waits on the CPU.
+    if (!all->gpu_idx || !local->gpu_idx) return fail(c, GNC_ERR_ARG, "gpu_idx is null");
+    const size_t cap = (((size_t)all->out_cap + c->world - 1) / c->world + 3) & ~(size_t)3;   // same on every rank
+    if (cap > c->gather_cap || !c->gather_buf) {
+      if (c->gather_buf) {
+        CUDA_TRY(c, cudaStreamSynchronize(stream));
+        CUDA_TRY(c, cudaFree(c->gather_buf));
+        c->gather_buf = nullptr;
+      }
+      CUDA_TRY(c, cudaMalloc((void**)&c->gather_buf, (size_t)c->world * (kSlotHeader + cap) * sizeof(uint32_t)));
+      c->gather_cap = cap;
+    }
+    const uint32_t slot_u32 = (uint32_t)(kSlotHeader + c->gather_cap);
+    uint32_t* mine = c->gather_buf + (size_t)c->rank * slot_u32;
+    const int blocks = 4 * c->sm_count;
+    gather_pack_kernel<<<blocks, 256, 0, stream>>>(local->counts, local->gpu_idx, mine, (uint32_t)c->gather_cap);
+    CUDA_TRY(c, cudaGetLastError());
+    NCCL_TRY(c, n->AllGather(mine, c->gather_buf, slot_u32, kNcclUint32, c->comm, stream));
+    gather_unpack_kernel<<<blocks, 256, 0, stream>>>(c->gather_buf, slot_u32, (uint32_t)c->gather_cap, c->world, all->gpu_idx,
+                                                     all->out_cap, all->counts);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches += 3;
+    return GNC_OK;
+  }
+  // Records too: offsets are needed on the host, so this path synchronises the stream once.
   // 1. every rank's counts block to every rank; the sum (exact, 128-bit for the key totals) is the
   //    all-reduce of the counts, and the per-rank GPU-node counts give the gather offsets
   NCCL_TRY(c, n->AllGather(local->counts, c->d_all_counts, GNC_N_COUNTS, kNcclInt64, c->comm, stream));

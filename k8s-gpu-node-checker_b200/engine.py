@@ -52,19 +52,22 @@ class DeviceResult:
     defer_cap: int
 
     @staticmethod
-    def alloc(n_nodes: int, device, out_cap: Optional[int] = None, defer_cap: int = 4096) -> "DeviceResult":
+    def alloc(n_nodes: int, device, out_cap: Optional[int] = None, defer_cap: int = 4096,
+              records: bool = True) -> "DeviceResult":
+        """`records=False` leaves gpu_total / gpu_vals out (a gather target that only wants the ordered indices)."""
         cap = max(1, n_nodes if out_cap is None else out_cap)
         return DeviceResult(torch.empty(max(1, n_nodes), dtype=torch.uint8, device=device),
                             torch.empty(cap, dtype=torch.int32, device=device),
-                            torch.empty(cap, dtype=torch.int64, device=device),
-                            torch.empty((cap, 4), dtype=torch.int64, device=device),
+                            torch.empty(cap if records else 0, dtype=torch.int64, device=device),
+                            torch.empty((cap if records else 0, 4), dtype=torch.int64, device=device),
                             torch.empty(max(1, defer_cap) * _DEFER_DT.itemsize, dtype=torch.uint8, device=device),
                             torch.zeros(N_COUNTS, dtype=torch.int64, device=device), cap, defer_cap)
 
     def c_struct(self) -> native.Result:
-        return native.Result(self.flags.data_ptr(), self.gpu_idx.data_ptr(), self.gpu_total.data_ptr(),
-                             self.gpu_vals.data_ptr(), self.defer.data_ptr(), self.counts.data_ptr(),
-                             self.out_cap, self.defer_cap)
+        return native.Result(self.flags.data_ptr(), self.gpu_idx.data_ptr(),
+                             self.gpu_total.data_ptr() if self.gpu_total.numel() else None,
+                             self.gpu_vals.data_ptr() if self.gpu_vals.numel() else None,
+                             self.defer.data_ptr(), self.counts.data_ptr(), self.out_cap, self.defer_cap)
 
 
 @dataclass
