@@ -143,6 +143,25 @@ int gnc_classify_host(gnc_ctx*, const gnc_batch* host_in, const gnc_result* host
 int gnc_classify_static(int device, const gnc_batch* in, const gnc_result* out, int max_str_digits,
                         void* cuda_stream, char* err, size_t err_cap);
 
+/* Raw /api/v1/nodes JSON bytes (DEVICE memory) -> PNL-v2 columns (DEVICE memory), ready for gnc_classify.
+ * Stands where the reference lets the kubernetes client fetch and deserialise the NodeList
+ * (api.list_node().items, check-gpu-node.py:217): only what the path reads is extracted -- each item's
+ * status.capacity entries (:183-187) and the type/status of its status.conditions (:173-177) -- with
+ * json.loads semantics (last duplicate key wins, \uXXXX escapes, surrogate pairs).  Non-string capacity
+ * values follow the client's dict(str,str) conversion: numbers keep their token (zero is falsy, skipped),
+ * true/false/null/containers never survive int(str(.)).  Asynchronous on `cuda_stream`.
+ * info[0] nodes, info[1] rows_bytes (= row_ptr[nodes]), info[2] status bits (1 no root "items" array,
+ * 2 nodes_cap too small, 4 rows_cap too small, 8 unbalanced JSON, 16 too many root-level arrays),
+ * info[3]/[4] byte positions of the items array's brackets. */
+typedef struct gnc_json_out {
+  uint8_t* rows;      /* [rows_cap], 16-byte aligned */
+  uint32_t* row_ptr;  /* [nodes_cap + 5], 16-byte aligned */
+  int64_t* info;      /* [8] */
+  uint64_t rows_cap;
+  uint32_t nodes_cap;
+} gnc_json_out;
+int gnc_json_to_pnl(gnc_ctx*, const uint8_t* json, uint64_t json_bytes, const gnc_json_out* out, void* cuda_stream);
+
 /* Kernels this context has launched since it was created (for benchmark accounting). */
 uint64_t gnc_launch_count(const gnc_ctx*);
 

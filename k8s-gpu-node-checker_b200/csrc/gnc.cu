@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "classify.cuh"
+#include "json_scan.cuh"
 
 using gnc::Params;
 using gnc::ScratchHeader;
@@ -84,6 +85,8 @@ struct gnc_ctx {
   void* comm = nullptr;
   int64_t* d_all_counts = nullptr;  // [world][GNC_N_COUNTS]
   int64_t* h_all_counts = nullptr;  // pinned
+  void* json_scratch = nullptr;     // gnc_json_to_pnl working arrays
+  size_t json_scratch_bytes = 0;
   uint32_t* gather_buf = nullptr;   // [world][32 + gather_cap] u32: counts block + indices of every rank
   size_t gather_cap = 0;
   std::string err;
@@ -452,6 +455,7 @@ extern "C" void gnc_destroy(gnc_ctx* c) {
     if (h.h_counts) cudaFreeHost(h.h_counts);
   }
   cudaFree(c->scratch);
+  cudaFree(c->json_scratch);
   delete c;
 }
 
@@ -805,5 +809,95 @@ extern "C" int gnc_classify_static(int device, const gnc_batch* in, const gnc_re
   const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(st.sm_count * st.ctas_per_sm[v]));
   var.launch(p, grid, var.smem, stream);
   STATIC_CUDA_TRY(cudaGetLastError());
+  return GNC_OK;
+}
+
+
+// =================================================================================================
+// Raw /api/v1/nodes JSON -> PNL-v2 on the device (include/gnc.h: gnc_json_to_pnl).
+// =================================================================================================
+namespace {
+
+template <class T, class Op>
+int device_exclusive_scan(gnc_ctx* c, const T* in, unsigned long long n, T* out, T* block_totals, T* grand, Op op, T ident,
+                          cudaStream_t stream) {
+  if (n == 0) {
+    if (grand) CUDA_TRY(c, cudaMemsetAsync(grand, 0, sizeof(T), stream));
+    return GNC_OK;
+  }
+  const unsigned long long nb = (n + 1023) / 1024;
+  gnc::js::scan_block_totals<T, Op><<<(unsigned)nb, 1024, 0, stream>>>(in, n, block_totals, op, ident);
+  gnc::js::scan_totals_serial<T, Op><<<1, 1, 0, stream>>>(block_totals, nb, op, ident, grand);
+  gnc::js::scan_apply<T, Op><<<(unsigned)nb, 1024, 0, stream>>>(in, n, block_totals, out, op, ident);
+  CUDA_TRY(c, cudaGetLastError());
+  c->launches += 3;
+  return GNC_OK;
+}
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_bytes, const gnc_json_out* out, void* cuda_stream) {
+  using namespace gnc::js;
+  if (!c) return GNC_ERR_ARG;
+  if (!json || !out || !out->rows || !out->row_ptr || !out->info) return fail(c, GNC_ERR_ARG, "null json or output buffer");
+  if (!aligned16(out->rows) || !aligned16(out->row_ptr)) return fail(c, GNC_ERR_ARG, "rows and row_ptr must be 16-byte aligned");
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  const unsigned long long n = json_bytes, n_chunks = (n + kChunk - 1) / kChunk, nodes_cap = out->nodes_cap;
+  if (n_chunks >= (1ull << 32)) return fail(c, GNC_ERR_ARG, "json document too large (1 TiB limit)");
+  // carve the working arrays out of one scratch allocation
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+  const size_t nbc = (n_chunks + 1023) / 1024 + 1, nbn = (nodes_cap + 1023) / 1024 + 1;
+  const size_t o_work = take(sizeof(Work)), o_funcs = take(n_chunks), o_pf = take(n_chunks), o_bt8 = take(nbc),
+               o_delta = take(n_chunks * 4), o_depth = take(n_chunks * 4), o_bt32 = take(nbc * 4), o_evc = take(n_chunks * 4),
+               o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
+               o_plain = take((nodes_cap + 1) * 8), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8);
+  if (off > c->json_scratch_bytes) {
+    if (c->json_scratch) {
+      CUDA_TRY(c, cudaStreamSynchronize(stream));
+      CUDA_TRY(c, cudaFree(c->json_scratch));
+      c->json_scratch = nullptr;
+      c->json_scratch_bytes = 0;
+    }
+    CUDA_TRY(c, cudaMalloc(&c->json_scratch, off + off / 8));
+    c->json_scratch_bytes = off + off / 8;
+  }
+  char* base = (char*)c->json_scratch;
+  Work* work = (Work*)(base + o_work);
+  uint8_t *funcs = (uint8_t*)(base + o_funcs), *pf = (uint8_t*)(base + o_pf), *bt8 = (uint8_t*)(base + o_bt8);
+  int *delta = (int*)(base + o_delta), *depth0 = (int*)(base + o_depth), *bt32 = (int*)(base + o_bt32);
+  unsigned int *evc = (unsigned int*)(base + o_evc), *evp = (unsigned int*)(base + o_evp), *btu = (unsigned int*)(base + o_btu);
+  unsigned long long *elem = (unsigned long long*)(base + o_elem), *plain = (unsigned long long*)(base + o_plain),
+                     *offs = (unsigned long long*)(base + o_offs), *bt64 = (unsigned long long*)(base + o_bt64),
+                     *total = (unsigned long long*)(base + o_total);
+  unsigned int* sizes = (unsigned int*)(base + o_sizes);
+  CUDA_TRY(c, cudaMemsetAsync(work, 0, sizeof(Work), stream));
+  int rc;
+  const unsigned cb = (unsigned)((n_chunks + 255) / 256);
+  if (n_chunks) {
+    lex_funcs_kernel<<<cb, 256, 0, stream>>>(json, n, funcs, n_chunks);
+    if ((rc = device_exclusive_scan<uint8_t, OpCompose>(c, funcs, n_chunks, pf, bt8, nullptr, OpCompose(), (uint8_t)kIdentity, stream))) return rc;
+    depth_delta_kernel<<<cb, 256, 0, stream>>>(json, n, pf, delta, n_chunks);
+    if ((rc = device_exclusive_scan<int, OpAddI>(c, delta, n_chunks, depth0, bt32, nullptr, OpAddI(), 0, stream))) return rc;
+    events_kernel<<<cb, 256, 0, stream>>>(json, n, pf, depth0, evc, work, n_chunks);
+    if ((rc = device_exclusive_scan<unsigned int, OpAddU>(c, evc, n_chunks, evp, btu, nullptr, OpAddU(), 0u, stream))) return rc;
+    pick_items_kernel<<<1, 1, 0, stream>>>(json, n, pf, depth0, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
+    element_starts_kernel<<<cb, 256, 0, stream>>>(json, n, pf, depth0, evp, work, elem, n_chunks);
+    c->launches += 5;
+  }
+  const unsigned nb = (unsigned)std::max<unsigned long long>(1, (nodes_cap + 127) / 128);
+  if (nodes_cap) {
+    CUDA_TRY(c, cudaMemsetAsync(sizes, 0, (nodes_cap + 1) * 4, stream));
+    measure_rows_kernel<<<nb, 128, 0, stream>>>(json, n, elem, work, sizes);
+    strip_flag_kernel<<<(unsigned)((nodes_cap + 255) / 256), 256, 0, stream>>>(sizes, plain, (unsigned int)nodes_cap);
+    c->launches += 2;
+  }
+  if ((rc = device_exclusive_scan<unsigned long long, OpAddULL>(c, plain, nodes_cap, offs, bt64, total, OpAddULL(), 0ull, stream))) return rc;
+  write_rows_kernel<<<nb, 128, 0, stream>>>(json, n, elem, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
+  CUDA_TRY(c, cudaGetLastError());
+  c->launches += 1;
   return GNC_OK;
 }

@@ -180,6 +180,28 @@ class Classifier:
         self._check(self.lib.gnc_gather(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.c_void_p(s.cuda_stream)))
         return fleet
 
+    # ---- raw JSON ingestion -------------------------------------------------------------------
+    def json_to_pnl(self, doc: torch.Tensor, nodes_cap: int, rows_cap: Optional[int] = None,
+                    stream: Optional[torch.cuda.Stream] = None) -> Tuple[DeviceBatch, torch.Tensor]:
+        """Raw /api/v1/nodes bytes (uint8 tensor on this GPU) -> (PNL-v2 shard in HBM, info[8]).
+
+        Synchronises once to read the node count and row bytes; raises on any status bit."""
+        s = stream or torch.cuda.current_stream(self.device)
+        rows_cap = int(rows_cap if rows_cap is not None else doc.numel() + 64)
+        rows = torch.empty(rows_cap, dtype=torch.uint8, device=self.device)
+        row_ptr = torch.empty(nodes_cap + 8, dtype=torch.int32, device=self.device)
+        info = torch.zeros(8, dtype=torch.int64, device=self.device)
+        out = native.JsonOut(rows.data_ptr(), row_ptr.data_ptr(), info.data_ptr(), rows_cap, nodes_cap)
+        self._check(self.lib.gnc_json_to_pnl(self._h, ctypes.c_void_p(doc.data_ptr()), doc.numel(), ctypes.byref(out),
+                                             ctypes.c_void_p(s.cuda_stream)))
+        h = info.cpu()
+        status = int(h[2])
+        if status:
+            names = {1: 'no root "items" array', 2: "nodes_cap too small", 4: "rows_cap too small", 8: "unbalanced JSON",
+                     16: "too many root-level arrays"}
+            raise native.GncError(-1, "gnc_json_to_pnl: " + ", ".join(v for k, v in names.items() if status & k))
+        return DeviceBatch(rows, row_ptr, int(h[0]), int(h[1])), h
+
     # ---- host-buffer path (what a binding without device memory of its own calls) ------------
     def classify_host(self, p: pnl.PackedNodeList, node_base: int = 0, defer_cap: int = 4096,
                       out: Optional[Dict[str, np.ndarray]] = None) -> Dict[str, np.ndarray]:

@@ -32,8 +32,13 @@ class Result(ctypes.Structure):
                 ("out_cap", ctypes.c_uint32), ("defer_cap", ctypes.c_uint32)]
 
 
+class JsonOut(ctypes.Structure):
+    _fields_ = [("rows", ctypes.c_void_p), ("row_ptr", ctypes.c_void_p), ("info", ctypes.c_void_p),
+                ("rows_cap", ctypes.c_uint64), ("nodes_cap", ctypes.c_uint32)]
+
+
 EXPORTS = ("gnc_abi_version", "gnc_create", "gnc_comm_id", "gnc_reserve", "gnc_set_max_str_digits", "gnc_classify",
-           "gnc_gather", "gnc_classify_host", "gnc_classify_static", "gnc_launch_count", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
+           "gnc_gather", "gnc_classify_host", "gnc_classify_static", "gnc_json_to_pnl", "gnc_launch_count", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
 
 
 class GncError(RuntimeError):
@@ -75,6 +80,8 @@ def lib() -> ctypes.CDLL:
     L.gnc_classify_static.argtypes = [i32, ctypes.POINTER(Batch), ctypes.POINTER(Result), i32, vp, ctypes.c_char_p,
                                       ctypes.c_size_t]
     L.gnc_classify_static.restype = i32
+    L.gnc_json_to_pnl.argtypes = [vp, vp, ctypes.c_uint64, ctypes.POINTER(JsonOut), vp]
+    L.gnc_json_to_pnl.restype = i32
     L.gnc_launch_count.argtypes = [vp]
     L.gnc_launch_count.restype = ctypes.c_uint64
     L.gnc_unicode_tables.argtypes = [ctypes.POINTER(ctypes.POINTER(u32)), ctypes.POINTER(i32),

@@ -289,3 +289,75 @@ def fleet(kind: str, seed: int, start: int, n: int):
     if kind == "g2":
         return g2_templates(), g2_tid(seed, start, n)
     raise ValueError(kind)
+
+
+# ----------------------------------------------------------------------------------------------
+# Config 5: fleets rendered as a raw /api/v1/nodes document.
+# ----------------------------------------------------------------------------------------------
+def node_json(spec: Dict[str, Any], payload: Optional[Dict[str, Any]] = None, style: int = 0) -> str:
+    """One element of `items` as the API server writes it (compact, Go struct field order).  `style`
+    > 0 decorates it with things a conforming parser must see through: whitespace, escaped key and
+    value spellings, duplicate keys (last wins), nested values to skip, non-string quantities."""
+    import json as _json
+    p = dict(spec)
+    p.update(payload or {})
+    def _u(s):                                                            # every character as \\uXXXX (pairs above the BMP)
+        out = []
+        for c in s:
+            cp = ord(c)
+            if cp > 0xFFFF:
+                cp -= 0x10000
+                out.append(f"\\u{0xD800 + (cp >> 10):04x}\\u{0xDC00 + (cp & 0x3FF):04x}")
+            else:
+                out.append(f"\\u{cp:04x}")
+        return "".join(out)
+    esc = _u if style & 2 else (lambda s: _json.dumps(s)[1:-1])
+    q = lambda s: '"' + (esc(s) if isinstance(s, str) else "") + '"'      # noqa: E731
+    sp = " \n\t " if style & 1 else ""
+    parts = []
+    if p.get("metadata", True) is not False:
+        md = {"name": p.get("name"), "labels": p.get("labels"), "annotations": {"note": "a \"quoted\" {brace} [bracket] \\ path"}}
+        parts.append('"metadata":' + sp + _json.dumps(md, ensure_ascii=bool(style & 2)))
+    if p.get("spec", True) is not False:
+        parts.append('"spec":' + _json.dumps({"taints": p.get("taints")}))
+    if p.get("status", True) is not False:
+        st = []
+        cap = p.get("capacity")
+        if style & 4 and cap is not None:                                 # decoys that must lose: an earlier duplicate, a look-alike
+            st.append('"capacity":{"nvidia.com/gpu":"64"}')
+            st.append('"capacityX":{"amd.com/gpu":"9"}')
+        if cap is not None:
+            ents = []
+            for k, v in cap:
+                if isinstance(v, str):
+                    ents.append(q(k) + ":" + sp + q(v))
+                else:
+                    ents.append(q(k) + ":" + _json.dumps(v))
+            st.append('"allocatable":{"nvidia.com/gpu":"1000"}')
+            st.append('"capacity":' + sp + "{" + ("," + sp).join(ents) + "}")
+        conds = p.get("conditions")
+        if conds is not None:
+            cs = []
+            for t, s_ in conds:
+                if isinstance(t, str) and t.startswith("plain:"):
+                    cs.append(_json.dumps([t[6:], s_]))                  # not an object: no V1NodeCondition comes of it
+                    continue
+                body = ['"lastHeartbeatTime":"2025-01-01T00:00:00Z"', '"type":' + (q(t) if isinstance(t, str) else "null"),
+                        '"status":' + (q(s_) if isinstance(s_, str) else "null"), '"reason":"Kubelet{Ready}","message":"ok, \\"fine\\""']
+                if style & 4:
+                    body.insert(0, '"status":"True","type":"Ready"')     # overwritten by the later type/status
+                cs.append("{" + ",".join(body) + "}")
+            st.append('"conditions":' + sp + "[" + ("," + sp).join(cs) + "]")
+        st.append('"nodeInfo":{"kubeletVersion":"v1.31.0","nested":{"deep":[1,2,{"x":"}]"}]}}')
+        parts.append('"status":' + sp + "{" + ",".join(st) + "}")
+    return "{" + ("," + sp).join(parts) + "}"
+
+
+def nodelist_json(templates: Sequence[Dict[str, Any]], tid, payload_fn=None, style_fn=None) -> bytes:
+    """A NodeList document for the fleet drawn from `templates` by `tid`."""
+    items = []
+    for i, t in enumerate(tid):
+        items.append(node_json(templates[int(t)], payload_fn(i, templates[int(t)]) if payload_fn else {"name": f"node-{i:08d}"},
+                               style_fn(i) if style_fn else 0))
+    head = '{"kind":"NodeList","apiVersion":"v1","metadata":{"resourceVersion":"12345","extra":[{"a":1},{"b":[{}]}]},"items":['
+    return (head + ",".join(items) + "]}").encode("utf-8", "surrogatepass")
