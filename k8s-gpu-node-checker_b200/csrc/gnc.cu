@@ -854,7 +854,7 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   const size_t o_work = take(sizeof(Work)), o_funcs = take(n_chunks), o_pf = take(n_chunks), o_bt8 = take(nbc),
                o_delta = take(n_chunks * 4), o_depth = take(n_chunks * 4), o_bt32 = take(nbc * 4), o_evc = take(n_chunks * 4),
                o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
-               o_plain = take((nodes_cap + 1) * 8), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8);
+               o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8);
   if (off > c->json_scratch_bytes) {
     if (c->json_scratch) {
       CUDA_TRY(c, cudaStreamSynchronize(stream));
@@ -874,6 +874,8 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
                      *offs = (unsigned long long*)(base + o_offs), *bt64 = (unsigned long long*)(base + o_bt64),
                      *total = (unsigned long long*)(base + o_total);
   unsigned int* sizes = (unsigned int*)(base + o_sizes);
+  NodePlan* plans = (NodePlan*)(base + o_plans);
+  if (!aligned16(json)) return fail(c, GNC_ERR_ARG, "json must be 16-byte aligned");
   CUDA_TRY(c, cudaMemsetAsync(work, 0, sizeof(Work), stream));
   int rc;
   const unsigned cb = (unsigned)((n_chunks + 255) / 256);
@@ -891,12 +893,12 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   const unsigned nb = (unsigned)std::max<unsigned long long>(1, (nodes_cap + 127) / 128);
   if (nodes_cap) {
     CUDA_TRY(c, cudaMemsetAsync(sizes, 0, (nodes_cap + 1) * 4, stream));
-    measure_rows_kernel<<<nb, 128, 0, stream>>>(json, n, elem, work, sizes);
+    measure_rows_kernel<<<nb, 128, 0, stream>>>(json, n, elem, work, sizes, plans);
     strip_flag_kernel<<<(unsigned)((nodes_cap + 255) / 256), 256, 0, stream>>>(sizes, plain, (unsigned int)nodes_cap);
     c->launches += 2;
   }
   if ((rc = device_exclusive_scan<unsigned long long, OpAddULL>(c, plain, nodes_cap, offs, bt64, total, OpAddULL(), 0ull, stream))) return rc;
-  write_rows_kernel<<<nb, 128, 0, stream>>>(json, n, elem, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
+  write_rows_kernel<<<nb, 128, 0, stream>>>(json, n, plans, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
   CUDA_TRY(c, cudaGetLastError());
   c->launches += 1;
   return GNC_OK;

@@ -52,18 +52,35 @@ __device__ __forceinline__ uint32_t compose(uint32_t f, uint32_t g) {  // first 
 }
 constexpr uint32_t kIdentity = 0 | (1 << 2) | (2 << 4);
 
+// Bytes of chunk c in order, fetched 16 at a time (the document is 16-byte aligned; the last,
+// partial chunk is read bytewise).
+template <class F>
+__device__ __forceinline__ void for_chunk_bytes(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long c, F&& f) {
+  const unsigned long long b = c * kChunk, e = min(n, b + kChunk);
+  if (e - b == kChunk) {
+    const uint4* v = reinterpret_cast<const uint4*>(json + b);
+#pragma unroll 4
+    for (int q = 0; q < kChunk / 16; q++) {
+      const uint4 x = __ldg(v + q);
+      const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+      for (int k = 0; k < 16; k++) f(b + 16 * q + k, (w[k >> 2] >> (8 * (k & 3))) & 0xFFu);
+    }
+  } else {
+    for (unsigned long long i = b; i < e; i++) f(i, (uint32_t)json[i]);
+  }
+}
+
 __global__ void lex_funcs_kernel(const uint8_t* __restrict__ json, unsigned long long n, uint8_t* __restrict__ funcs,
                                  unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
   if (c >= n_chunks) return;
-  const unsigned long long b = c * kChunk, e = min(n, b + kChunk);
   int s0 = 0, s1 = 1, s2 = 2;
-  for (unsigned long long i = b; i < e; i++) {
-    const uint32_t ch = json[i];
+  for_chunk_bytes(json, n, c, [&](unsigned long long, uint32_t ch) {
     s0 = lex_step(s0, ch);
     s1 = lex_step(s1, ch);
     s2 = lex_step(s2, ch);
-  }
+  });
   funcs[c] = (uint8_t)(s0 | (s1 << 2) | (s2 << 4));
 }
 
@@ -131,9 +148,7 @@ __device__ __forceinline__ int start_state(const uint8_t* prefix_funcs, unsigned
 template <class F>
 __device__ __forceinline__ int visit_chunk(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long c, int st,
                                            int depth, F&& f) {
-  const unsigned long long b = c * kChunk, e = min(n, b + kChunk);
-  for (unsigned long long i = b; i < e; i++) {
-    const uint32_t ch = json[i];
+  for_chunk_bytes(json, n, c, [&](unsigned long long i, uint32_t ch) {
     if (st == 0) {
       if (ch == '"') {
         st = 1;
@@ -145,7 +160,7 @@ __device__ __forceinline__ int visit_chunk(const uint8_t* __restrict__ json, uns
     } else {
       st = lex_step(st, ch);
     }
-  }
+  });
   return depth;
 }
 
@@ -569,8 +584,15 @@ __device__ void emit_conditions(Cur c, RowOut& o) {  // cursor at '[' of the con
   }
 }
 
-// Parse the element starting at `pos`; measure or write its row.
-__device__ void node_row(const uint8_t* json, unsigned long long n, unsigned long long pos, RowOut& o) {
+// What the measuring pass learns about a node and the writing pass reuses.
+struct NodePlan {
+  unsigned long long cap_pos, cond_pos;  // '{' of status.capacity and '[' of status.conditions, ~0 if none
+  unsigned int n_cap, n_cond;
+};
+
+// Locate the element's status.capacity object and status.conditions array (last duplicates win).
+__device__ void node_locate(const uint8_t* json, unsigned long long n, unsigned long long pos, NodePlan& pl) {
+  pl.cap_pos = pl.cond_pos = ~0ull;
   Cur c{json, pos, n};
   c.ws();
   if (c.peek() != '{') return;                                  // not an object: an empty node
@@ -582,24 +604,27 @@ __device__ void node_row(const uint8_t* json, unsigned long long n, unsigned lon
   Cur a = c, b = c;
   const unsigned long long cap = find_last_member(a, "capacity", 8);
   const unsigned long long cond = find_last_member(b, "conditions", 10);
-  if (cap != ~0ull) {
-    Cur q{json, cap, n};
-    if (q.peek() == '{') emit_capacity(q, o);
-  }
-  if (cond != ~0ull) {
-    Cur q{json, cond, n};
-    if (q.peek() == '[') emit_conditions(q, o);
-  }
+  if (cap != ~0ull && json[cap] == '{') pl.cap_pos = cap;
+  if (cond != ~0ull && json[cond] == '[') pl.cond_pos = cond;
+}
+__device__ void node_emit(const uint8_t* json, unsigned long long n, const NodePlan& pl, RowOut& o) {
+  if (pl.cap_pos != ~0ull) emit_capacity(Cur{json, pl.cap_pos, n}, o);
+  if (pl.cond_pos != ~0ull) emit_conditions(Cur{json, pl.cond_pos, n}, o);
 }
 
 // row size in bytes (4-byte padded); bit 31 set when the extended form is needed
 __global__ void measure_rows_kernel(const uint8_t* __restrict__ json, unsigned long long n, const unsigned long long* __restrict__ elem_pos,
-                                    const Work* w, unsigned int* __restrict__ sizes) {
+                                    const Work* w, unsigned int* __restrict__ sizes, NodePlan* __restrict__ plans) {
   const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= w->n_nodes) return;
   RowOut o{};
   o.write = false;
-  node_row(json, min(n, w->items_end), elem_pos[i], o);
+  NodePlan pl;
+  node_locate(json, min(n, w->items_end), elem_pos[i], pl);
+  node_emit(json, min(n, w->items_end), pl, o);
+  pl.n_cap = (unsigned int)o.n_cap;
+  pl.n_cond = (unsigned int)o.n_cond;
+  plans[i] = pl;
   const bool ext = o.n_cap >= 255 || o.n_cond >= 255 || o.maxlen >= 255;
   unsigned long long bytes = ext ? 12 + 8 * (o.n_cap + o.n_cond) + o.text : 2 + 2 * (o.n_cap + o.n_cond) + o.text;
   bytes = (bytes + 3) & ~3ull;
@@ -611,7 +636,7 @@ __global__ void strip_flag_kernel(const unsigned int* __restrict__ sizes, unsign
   if (i < n) plain[i] = sizes[i] & 0x7FFFFFFFu;
 }
 
-__global__ void write_rows_kernel(const uint8_t* __restrict__ json, unsigned long long n, const unsigned long long* __restrict__ elem_pos,
+__global__ void write_rows_kernel(const uint8_t* __restrict__ json, unsigned long long n, const NodePlan* __restrict__ plans,
                                   const Work* w, const unsigned int* __restrict__ sizes, const unsigned long long* __restrict__ offs,
                                   const unsigned long long* __restrict__ total, uint8_t* __restrict__ rows, unsigned long long rows_cap,
                                   uint32_t* __restrict__ row_ptr, long long* __restrict__ info) {
@@ -641,11 +666,8 @@ __global__ void write_rows_kernel(const uint8_t* __restrict__ json, unsigned lon
   o.write = true;
   o.row = row;
   o.ext = (sizes[i] >> 31) != 0;
-  // entry counts are needed before the table can be placed: measure again (cheap next to the copy)
-  RowOut m{};
-  m.write = false;
-  node_row(json, min(n, w->items_end), elem_pos[i], m);
-  const unsigned long long ne = m.n_cap + m.n_cond;
+  const NodePlan m = plans[i];
+  const unsigned long long ne = (unsigned long long)m.n_cap + m.n_cond;
   if (o.ext) {
     row[0] = row[1] = 0xFF;
     uint32_t a = (uint32_t)m.n_cap, b = (uint32_t)m.n_cond;
@@ -657,7 +679,7 @@ __global__ void write_rows_kernel(const uint8_t* __restrict__ json, unsigned lon
     row[1] = (uint8_t)m.n_cond;
     o.text_off = 2 + 2 * ne;
   }
-  node_row(json, min(n, w->items_end), elem_pos[i], o);
+  node_emit(json, min(n, w->items_end), m, o);
 }
 
 }  // namespace js
