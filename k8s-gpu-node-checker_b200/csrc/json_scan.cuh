@@ -457,6 +457,44 @@ __device__ unsigned long long find_last_member(Cur& c, const char* lit, int len)
   return found;
 }
 
+// Same for two names in one pass over the object (each: the LAST member of that name, or ~0).
+__device__ void find_last_members2(Cur& c, const char* lit_a, int len_a, const char* lit_b, int len_b,
+                                   unsigned long long* pos_a, unsigned long long* pos_b) {
+  *pos_a = *pos_b = ~0ull;
+  c.i++;  // '{'
+  while (true) {
+    c.ws();
+    int ch = c.peek();
+    if (ch == '}') {
+      c.i++;
+      break;
+    }
+    if (ch == ',') {
+      c.i++;
+      continue;
+    }
+    if (ch != '"') break;
+    // decode the key once, comparing against both names
+    c.i++;
+    StrReader r(&c);
+    int k = 0;
+    bool ea = true, eb = true;
+    for (int b = r.next(); b >= 0; b = r.next(), k++) {
+      ea = ea && k < len_a && b == (uint8_t)lit_a[k];
+      eb = eb && k < len_b && b == (uint8_t)lit_b[k];
+    }
+    ea = ea && k == len_a;
+    eb = eb && k == len_b;
+    c.ws();
+    if (c.peek() != ':') break;
+    c.i++;
+    c.ws();
+    if (ea) *pos_a = c.i;
+    if (eb) *pos_b = c.i;
+    skip_value(c);
+  }
+}
+
 // value at the cursor as a capacity quantity: how many bytes the PNL value has
 //   string -> decoded text; number -> its token, or nothing when it is zero (a falsy value is
 //   skipped, check-gpu-node.py:188); true/false/null/containers -> nothing (int(str(.)) fails or falsy)
@@ -557,10 +595,8 @@ __device__ void emit_conditions(Cur c, RowOut& o) {  // cursor at '[' of the con
       skip_value(c);
       continue;
     }
-    Cur a = c, b = c;
-    const unsigned long long tpos = find_last_member(a, "type", 4);
-    const unsigned long long spos = find_last_member(b, "status", 6);
-    c = a;  // after the object
+    unsigned long long tpos, spos;
+    find_last_members2(c, "type", 4, "status", 6, &tpos, &spos);  // leaves c after the object
     Cur t = c, s = c;
     unsigned long long tl = 0, sl = 0;
     if (tpos != ~0ull) {
@@ -601,9 +637,8 @@ __device__ void node_locate(const uint8_t* json, unsigned long long n, unsigned 
   if (st == ~0ull) return;
   c.i = st;
   if (c.peek() != '{') return;                                  // null / other: status falsy
-  Cur a = c, b = c;
-  const unsigned long long cap = find_last_member(a, "capacity", 8);
-  const unsigned long long cond = find_last_member(b, "conditions", 10);
+  unsigned long long cap, cond;
+  find_last_members2(c, "capacity", 8, "conditions", 10, &cap, &cond);
   if (cap != ~0ull && json[cap] == '{') pl.cap_pos = cap;
   if (cond != ~0ull && json[cond] == '[') pl.cond_pos = cond;
 }
