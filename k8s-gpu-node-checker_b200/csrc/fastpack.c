@@ -1,0 +1,379 @@
+/* _fastpack -- CPython extension: V1Node objects -> PNL-v2 columns.
+ *
+ * The same marshalling as pnl.node_row / pnl.encode_row (the attribute reads of
+ * check-gpu-node.py:173-176, :183-187), without a Python-level loop per entry:
+ *     pack_nodes(nodes, condition_class) -> (rows: bytes, row_ptr: bytes /u32 little-endian/, n_nodes)
+ * rows carries ROWS_PAD zero bytes and row_ptr ROWPTR_PAD repeats of the total after the last valid
+ * element, as the device buffers require.  Type adaptation only; nothing is classified here.
+ */
+#define PY_SSIZE_T_CLEAN
+#include <Python.h>
+#include <stdint.h>
+#include <string.h>
+
+#define ROWS_PAD 32
+#define ROWPTR_PAD 4
+
+typedef struct {
+  char* p;
+  size_t n, cap;
+} buf_t;
+
+static int buf_reserve(buf_t* b, size_t extra) {
+  if (b->n + extra <= b->cap) return 0;
+  size_t cap = b->cap ? b->cap : 1 << 16;
+  while (cap < b->n + extra) cap *= 2;
+  char* q = (char*)realloc(b->p, cap);
+  if (!q) {
+    PyErr_NoMemory();
+    return -1;
+  }
+  b->p = q;
+  b->cap = cap;
+  return 0;
+}
+static int buf_put(buf_t* b, const void* src, size_t len) {
+  if (buf_reserve(b, len)) return -1;
+  memcpy(b->p + b->n, src, len);
+  b->n += len;
+  return 0;
+}
+
+/* UTF-8 bytes of a str with 'surrogatepass' semantics; *owner must be DECREF'd when non-NULL. */
+static int utf8_of(PyObject* s, const char** data, Py_ssize_t* len, PyObject** owner) {
+  *owner = NULL;
+  *data = PyUnicode_AsUTF8AndSize(s, len);
+  if (*data) return 0;
+  PyErr_Clear(); /* lone surrogates: the strict codec refuses them */
+  *owner = PyUnicode_AsEncodedString(s, "utf-8", "surrogatepass");
+  if (!*owner) return -1;
+  *data = PyBytes_AS_STRING(*owner);
+  *len = PyBytes_GET_SIZE(*owner);
+  return 0;
+}
+
+typedef struct {
+  const char* k;
+  Py_ssize_t kl;
+  const char* v;
+  Py_ssize_t vl;
+  PyObject* ko;
+  PyObject* vo; /* owners (may be NULL) */
+} entry_t;
+
+typedef struct {
+  entry_t* e;
+  size_t n, cap;
+} entries_t;
+
+static int entries_push(entries_t* es, entry_t* en) {
+  if (es->n == es->cap) {
+    size_t cap = es->cap ? es->cap * 2 : 32;
+    entry_t* q = (entry_t*)realloc(es->e, cap * sizeof(entry_t));
+    if (!q) {
+      PyErr_NoMemory();
+      return -1;
+    }
+    es->e = q;
+    es->cap = cap;
+  }
+  es->e[es->n++] = *en;
+  return 0;
+}
+static void entries_clear(entries_t* es) {
+  for (size_t i = 0; i < es->n; i++) {
+    Py_XDECREF(es->e[i].ko);
+    Py_XDECREF(es->e[i].vo);
+  }
+  es->n = 0;
+}
+
+/* A capacity value as the device will parse it: str as is; otherwise "" when falsy, str(value) when
+ * truthy, "?" when either raises (the reference's try block swallows it, check-gpu-node.py:188-195). */
+static int quantity_of(PyObject* v, entry_t* en) {
+  if (PyUnicode_Check(v)) return utf8_of(v, &en->v, &en->vl, &en->vo);
+  int truth = PyObject_IsTrue(v);
+  if (truth == 0) {
+    en->v = "";
+    en->vl = 0;
+    return 0;
+  }
+  if (truth > 0) {
+    PyObject* s = PyObject_Str(v);
+    if (s) {
+      const char* d;
+      Py_ssize_t l;
+      PyObject* o;
+      if (utf8_of(s, &d, &l, &o) == 0) {
+        if (o) {
+          Py_DECREF(s);
+          en->vo = o;
+        } else {
+          en->vo = s; /* the str owns its cached UTF-8 */
+        }
+        en->v = d;
+        en->vl = l;
+        return 0;
+      }
+      Py_DECREF(s);
+    }
+  }
+  PyErr_Clear();
+  en->v = "?";
+  en->vl = 1;
+  return 0;
+}
+
+static PyObject *s_status, *s_capacity, *s_conditions, *s_type, *s_items;
+
+static int collect(PyObject* node, PyObject* cond_cls, entries_t* caps, entries_t* conds) {
+  PyObject* st = PyObject_GetAttr(node, s_status);
+  if (!st) return -1;
+  int t = PyObject_IsTrue(st);
+  if (t <= 0) {
+    Py_DECREF(st);
+    return t;
+  }
+  PyObject* cap = PyObject_GetAttr(st, s_capacity);
+  if (!cap) {
+    Py_DECREF(st);
+    return -1;
+  }
+  t = PyObject_IsTrue(cap);
+  if (t < 0) goto fail_cap;
+  if (t) {
+    PyObject* items = PyDict_CheckExact(cap) ? NULL : PyObject_CallMethodNoArgs(cap, s_items);
+    if (!PyDict_CheckExact(cap) && !items) goto fail_cap;
+    PyObject *k, *v;
+    if (!items) {
+      Py_ssize_t pos = 0;
+      while (PyDict_Next(cap, &pos, &k, &v)) {
+        if (!PyUnicode_Check(k)) continue; /* cannot equal any of the four str keys */
+        entry_t en = {0};
+        if (utf8_of(k, &en.k, &en.kl, &en.ko) || quantity_of(v, &en) || entries_push(caps, &en)) goto fail_cap;
+      }
+    } else {
+      PyObject* it = PyObject_GetIter(items);
+      Py_DECREF(items);
+      if (!it) goto fail_cap;
+      PyObject* pair;
+      while ((pair = PyIter_Next(it))) {
+        if (!PyTuple_Check(pair) || PyTuple_GET_SIZE(pair) != 2) {
+          Py_DECREF(pair);
+          continue;
+        }
+        k = PyTuple_GET_ITEM(pair, 0);
+        v = PyTuple_GET_ITEM(pair, 1);
+        if (PyUnicode_Check(k)) {
+          entry_t en = {0};
+          /* keep the pair alive through the owners: take strong refs */
+          if (utf8_of(k, &en.k, &en.kl, &en.ko) || quantity_of(v, &en)) {
+            Py_DECREF(pair);
+            Py_DECREF(it);
+            goto fail_cap;
+          }
+          if (!en.ko) {
+            Py_INCREF(k);
+            en.ko = k;
+          }
+          if (!en.vo && PyUnicode_Check(v)) {
+            Py_INCREF(v);
+            en.vo = v;
+          }
+          if (entries_push(caps, &en)) {
+            Py_DECREF(pair);
+            Py_DECREF(it);
+            goto fail_cap;
+          }
+        }
+        Py_DECREF(pair);
+      }
+      Py_DECREF(it);
+      if (PyErr_Occurred()) goto fail_cap;
+    }
+  }
+  Py_DECREF(cap);
+  {
+    PyObject* cl = PyObject_GetAttr(st, s_conditions);
+    if (!cl) {
+      Py_DECREF(st);
+      return -1;
+    }
+    t = PyObject_IsTrue(cl);
+    if (t < 0) {
+      Py_DECREF(cl);
+      Py_DECREF(st);
+      return -1;
+    }
+    if (t) {
+      PyObject* it = PyObject_GetIter(cl);
+      if (!it) {
+        Py_DECREF(cl);
+        Py_DECREF(st);
+        return -1;
+      }
+      PyObject* c;
+      while ((c = PyIter_Next(it))) {
+        int is = PyObject_IsInstance(c, cond_cls); /* check-gpu-node.py:176 */
+        if (is < 0) {
+          Py_DECREF(c);
+          Py_DECREF(it);
+          Py_DECREF(cl);
+          Py_DECREF(st);
+          return -1;
+        }
+        if (is) {
+          entry_t en = {0};
+          PyObject* ty = PyObject_GetAttr(c, s_type);
+          PyObject* su = ty ? PyObject_GetAttr(c, s_status) : NULL;
+          int bad = !ty || !su;
+          if (!bad) {
+            if (PyUnicode_Check(ty)) {
+              bad = utf8_of(ty, &en.k, &en.kl, &en.ko);
+              if (!bad && !en.ko) {
+                Py_INCREF(ty);
+                en.ko = ty;
+              }
+            } else {
+              en.k = "";
+            }
+            if (!bad && PyUnicode_Check(su)) {
+              bad = utf8_of(su, &en.v, &en.vl, &en.vo);
+              if (!bad && !en.vo) {
+                Py_INCREF(su);
+                en.vo = su;
+              }
+            } else if (!bad) {
+              en.v = "";
+            }
+          }
+          Py_XDECREF(ty);
+          Py_XDECREF(su);
+          if (bad || entries_push(conds, &en)) {
+            Py_DECREF(c);
+            Py_DECREF(it);
+            Py_DECREF(cl);
+            Py_DECREF(st);
+            return -1;
+          }
+        }
+        Py_DECREF(c);
+      }
+      Py_DECREF(it);
+      if (PyErr_Occurred()) {
+        Py_DECREF(cl);
+        Py_DECREF(st);
+        return -1;
+      }
+    }
+    Py_DECREF(cl);
+  }
+  Py_DECREF(st);
+  return 0;
+fail_cap:
+  Py_DECREF(cap);
+  Py_DECREF(st);
+  return -1;
+}
+
+static int emit_row(buf_t* rows, entries_t* caps, entries_t* conds) {
+  const size_t n = caps->n + conds->n;
+  int ext = caps->n >= 255 || conds->n >= 255;
+  size_t text = 0;
+  for (int part = 0; part < 2; part++) {
+    entries_t* es = part ? conds : caps;
+    for (size_t i = 0; i < es->n; i++) {
+      if (es->e[i].kl >= 255 || es->e[i].vl >= 255) ext = 1;
+      text += (size_t)es->e[i].kl + (size_t)es->e[i].vl;
+    }
+  }
+  const size_t head = ext ? 12 + 8 * n : 2 + 2 * n;
+  const size_t total = (head + text + 3) & ~(size_t)3;
+  if (buf_reserve(rows, total)) return -1;
+  unsigned char* row = (unsigned char*)rows->p + rows->n;
+  memset(row, 0, total);
+  if (ext) {
+    uint32_t a = (uint32_t)caps->n, b = (uint32_t)conds->n;
+    row[0] = row[1] = 0xFF;
+    memcpy(row + 4, &a, 4);
+    memcpy(row + 8, &b, 4);
+  } else {
+    row[0] = (unsigned char)caps->n;
+    row[1] = (unsigned char)conds->n;
+  }
+  size_t k = 0, off = head;
+  for (int part = 0; part < 2; part++) {
+    entries_t* es = part ? conds : caps;
+    for (size_t i = 0; i < es->n; i++, k++) {
+      const entry_t* en = &es->e[i];
+      if (ext) {
+        uint32_t a = (uint32_t)en->kl, b = (uint32_t)en->vl;
+        memcpy(row + 12 + 8 * k, &a, 4);
+        memcpy(row + 12 + 8 * k + 4, &b, 4);
+      } else {
+        row[2 + 2 * k] = (unsigned char)en->kl;
+        row[2 + 2 * k + 1] = (unsigned char)en->vl;
+      }
+      memcpy(row + off, en->k, (size_t)en->kl);
+      memcpy(row + off + en->kl, en->v, (size_t)en->vl);
+      off += (size_t)en->kl + (size_t)en->vl;
+    }
+  }
+  rows->n += total;
+  return 0;
+}
+
+static PyObject* pack_nodes(PyObject* self, PyObject* args) {
+  PyObject *nodes, *cond_cls;
+  if (!PyArg_ParseTuple(args, "OO", &nodes, &cond_cls)) return NULL;
+  PyObject* seq = PySequence_Fast(nodes, "nodes must be a sequence");
+  if (!seq) return NULL;
+  const Py_ssize_t n = PySequence_Fast_GET_SIZE(seq);
+  buf_t rows = {0}, ptr = {0};
+  entries_t caps = {0}, conds = {0};
+  PyObject* result = NULL;
+  uint32_t zero = 0;
+  if (buf_put(&ptr, &zero, 4)) goto done;
+  for (Py_ssize_t i = 0; i < n; i++) {
+    entries_clear(&caps);
+    entries_clear(&conds);
+    if (collect(PySequence_Fast_GET_ITEM(seq, i), cond_cls, &caps, &conds) < 0) goto done;
+    if (emit_row(&rows, &caps, &conds)) goto done;
+    if (rows.n > 0xFFF00000u) {
+      PyErr_SetString(PyExc_ValueError, "PNL-v2 rows are limited to 4 GiB - 1 MiB per list; split the fleet");
+      goto done;
+    }
+    uint32_t end = (uint32_t)rows.n;
+    if (buf_put(&ptr, &end, 4)) goto done;
+  }
+  {
+    uint32_t end = (uint32_t)rows.n;
+    char pad[ROWS_PAD] = {0};
+    if (buf_put(&rows, pad, ROWS_PAD)) goto done;
+    for (int k = 0; k < ROWPTR_PAD; k++)
+      if (buf_put(&ptr, &end, 4)) goto done;
+    result = Py_BuildValue("(y#y#n)", rows.p ? rows.p : "", (Py_ssize_t)rows.n, ptr.p, (Py_ssize_t)ptr.n, n);
+  }
+done:
+  entries_clear(&caps);
+  entries_clear(&conds);
+  free(caps.e);
+  free(conds.e);
+  free(rows.p);
+  free(ptr.p);
+  Py_DECREF(seq);
+  return result;
+}
+
+static PyMethodDef methods[] = {{"pack_nodes", pack_nodes, METH_VARARGS, "V1Node objects -> (rows bytes, row_ptr bytes, n)"},
+                                {NULL, NULL, 0, NULL}};
+static struct PyModuleDef moddef = {PyModuleDef_HEAD_INIT, "_fastpack", "PNL-v2 packer (C)", -1, methods};
+
+PyMODINIT_FUNC PyInit__fastpack(void) {
+  s_status = PyUnicode_InternFromString("status");
+  s_capacity = PyUnicode_InternFromString("capacity");
+  s_conditions = PyUnicode_InternFromString("conditions");
+  s_type = PyUnicode_InternFromString("type");
+  s_items = PyUnicode_InternFromString("items");
+  return PyModule_Create(&moddef);
+}

@@ -57,6 +57,16 @@ def build(verbose: bool = False) -> str:
     return LIB_PATH
 
 
+def build_fastpack() -> str:
+    """Compile csrc/fastpack.c (the C packer for V1Node objects) next to the package's Python files."""
+    import sysconfig
+    out = os.path.join(HERE, "_fastpack" + sysconfig.get_config_var("EXT_SUFFIX"))
+    cmd = ["gcc", "-O2", "-fPIC", "-shared", "-Wall", "-I" + sysconfig.get_paths()["include"],
+           os.path.join(CSRC, "fastpack.c"), "-o", out]
+    subprocess.check_call(cmd)
+    return out
+
+
 _lib = None
 
 
