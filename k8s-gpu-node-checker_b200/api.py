@@ -74,6 +74,23 @@ def summary_json(gpu_nodes: List[Dict], ready_gpu_nodes: List[Dict]) -> str:
                       ensure_ascii=False, indent=2)
 
 
+def summary_json_from_result(nodes: Sequence[Any], res: engine.FleetResult) -> str:
+    """The same `--json` text straight from the device's decisions (check-gpu-node.py:273-279), written
+    by the C emitter without building the list of dicts; falls back to build_records + json.dumps when
+    the extension is not built or a payload value has a type it does not format."""
+    fp = pnl._fastpack()
+    if fp is not None:
+        wide = {n: (sum(bd.values()), bd) for n, bd in res.wide.items()} if res.wide else None
+        totals = np.array([t if -2 ** 63 <= t < 2 ** 63 else 0 for t in res.gpu_total], dtype=np.int64) \
+            if res.wide else np.asarray(res.gpu_total, dtype=np.int64)
+        txt = fp.emit_summary_json(nodes, np.ascontiguousarray(res.gpu_idx, dtype=np.int64), np.ascontiguousarray(res.flags),
+                                   totals, np.ascontiguousarray(res.gpu_vals, dtype=np.int64).reshape(-1), wide, res.node_base)
+        if txt is not None:
+            return txt
+    g, r = build_records(nodes, res)
+    return summary_json(g, r)
+
+
 def exit_code(gpu_nodes: List[Dict], ready_gpu_nodes: List[Dict]) -> int:
     """check-gpu-node.py:289-293."""
     if ready_gpu_nodes:

@@ -365,7 +365,250 @@ done:
   return result;
 }
 
-static PyMethodDef methods[] = {{"pack_nodes", pack_nodes, METH_VARARGS, "V1Node objects -> (rows bytes, row_ptr bytes, n)"},
+
+/* ------------------------------------------------------------------------------------------------
+ * emit_summary_json: the `--json` document of check-gpu-node.py:273-279, i.e. exactly the text of
+ *   json.dumps({"total_nodes": G, "ready_nodes": R, "nodes": [...]}, ensure_ascii=False, indent=2)
+ * written straight from the device's decisions and each GPU node's payload, without building the
+ * list of dicts or a Python-level loop per node.
+ *   emit_summary_json(nodes, gpu_idx: int64 buffer[G], flags: uint8 buffer[N], totals: int64 buffer[G],
+ *                     vals: int64 buffer[G*4], wide: dict node -> (gpus:int, breakdown:dict) | None, node_base)
+ * Returns str, or None when some payload value is of a type this writer does not format (the caller
+ * then uses json.dumps). */
+static const char* const KEY_NAMES[4] = {"nvidia.com/gpu", "amd.com/gpu", "gpu.intel.com/i915", "intel.com/gpu"};
+
+static int put_s(buf_t* b, const char* s) { return buf_put(b, s, strlen(s)); }
+/* json.dumps string rules with ensure_ascii=False */
+static int put_json_str(buf_t* b, PyObject* s) {
+  const char* d;
+  Py_ssize_t n;
+  PyObject* owner;
+  if (utf8_of(s, &d, &n, &owner)) return -1;
+  int rc = buf_put(b, "\"", 1);
+  Py_ssize_t run = 0;
+  for (Py_ssize_t i = 0; i < n && !rc; i++) {
+    const unsigned char c = (unsigned char)d[i];
+    const char* esc = NULL;
+    char tmp[8];
+    switch (c) {
+      case '"': esc = "\\\""; break;
+      case '\\': esc = "\\\\"; break;
+      case '\n': esc = "\\n"; break;
+      case '\r': esc = "\\r"; break;
+      case '\t': esc = "\\t"; break;
+      case '\b': esc = "\\b"; break;
+      case '\f': esc = "\\f"; break;
+      default:
+        if (c < 0x20) {
+          snprintf(tmp, sizeof tmp, "\\u%04x", c);
+          esc = tmp;
+        }
+    }
+    if (esc) {
+      rc = buf_put(b, d + run, (size_t)(i - run)) || put_s(b, esc);
+      run = i + 1;
+    }
+  }
+  if (!rc) rc = buf_put(b, d + run, (size_t)(n - run)) || buf_put(b, "\"", 1);
+  Py_XDECREF(owner);
+  return rc;
+}
+/* 1 written, 0 unsupported type, -1 error */
+static int put_scalar(buf_t* b, PyObject* v) {
+  if (v == Py_None) return put_s(b, "null") ? -1 : 1;
+  if (PyUnicode_Check(v)) return put_json_str(b, v) ? -1 : 1;
+  if (v == Py_True) return put_s(b, "true") ? -1 : 1;
+  if (v == Py_False) return put_s(b, "false") ? -1 : 1;
+  if (PyLong_CheckExact(v)) {
+    PyObject* t = PyObject_Str(v);
+    if (!t) return -1;
+    Py_ssize_t n;
+    const char* d = PyUnicode_AsUTF8AndSize(t, &n);
+    int rc = d ? buf_put(b, d, (size_t)n) : -1;
+    Py_DECREF(t);
+    return rc ? -1 : 1;
+  }
+  return 0;
+}
+static int put_i64(buf_t* b, long long v) {
+  char tmp[32];
+  snprintf(tmp, sizeof tmp, "%lld", v);
+  return put_s(b, tmp);
+}
+
+static PyObject *s_metadata, *s_name, *s_labels, *s_spec, *s_taints, *s_key, *s_value, *s_effect;
+
+static PyObject* emit_summary_json(PyObject* self, PyObject* args) {
+  PyObject *nodes, *wide;
+  Py_buffer idx, flags, totals, vals;
+  long long node_base;
+  if (!PyArg_ParseTuple(args, "Oy*y*y*y*OL", &nodes, &idx, &flags, &totals, &vals, &wide, &node_base)) return NULL;
+  PyObject* seq = PySequence_Fast(nodes, "nodes must be a sequence");
+  PyObject* result = NULL;
+  buf_t b = {0};
+  int unsupported = 0;
+  if (!seq) goto done;
+  {
+    const Py_ssize_t g = idx.len / 8, n_nodes = PySequence_Fast_GET_SIZE(seq);
+    const long long* gi = (const long long*)idx.buf;
+    const long long* gt = (const long long*)totals.buf;
+    const long long* gv = (const long long*)vals.buf;
+    const unsigned char* fl = (const unsigned char*)flags.buf;
+    long long ready = 0;
+    for (Py_ssize_t i = 0; i < g; i++) ready += (fl[gi[i] - node_base] >> 1) & 1;
+    if (put_s(&b, "{\n  \"total_nodes\": ") || put_i64(&b, (long long)g) || put_s(&b, ",\n  \"ready_nodes\": ") ||
+        put_i64(&b, ready) || put_s(&b, ",\n  \"nodes\": ["))
+      goto done;
+    if (g == 0 && put_s(&b, "]")) goto done;
+    for (Py_ssize_t i = 0; i < g && !unsupported; i++) {
+      const long long node_i = gi[i];
+      if (node_i - node_base < 0 || node_i - node_base >= n_nodes) {
+        PyErr_SetString(PyExc_IndexError, "gpu_idx outside the node list");
+        goto done;
+      }
+      PyObject* node = PySequence_Fast_GET_ITEM(seq, node_i - node_base);
+      const unsigned f = fl[node_i - node_base];
+      if (put_s(&b, i ? ",\n    {\n      \"name\": " : "\n    {\n      \"name\": ")) goto done;
+      /* name / labels: check-gpu-node.py:203, :207 */
+      PyObject* md = PyObject_GetAttr(node, s_metadata);
+      if (!md) goto done;
+      int md_true = PyObject_IsTrue(md);
+      PyObject* labels = NULL;
+      if (md_true > 0) {
+        PyObject* nm = PyObject_GetAttr(md, s_name);
+        labels = nm ? PyObject_GetAttr(md, s_labels) : NULL;
+        int rc = (nm && labels) ? put_scalar(&b, nm) : -1;
+        Py_XDECREF(nm);
+        if (rc < 0) { Py_XDECREF(labels); Py_DECREF(md); goto done; }
+        if (rc == 0) unsupported = 1;
+      } else if (md_true == 0) {
+        if (put_s(&b, "\"\"")) { Py_DECREF(md); goto done; }
+      } else { Py_DECREF(md); goto done; }
+      Py_DECREF(md);
+      if (put_s(&b, ",\n      \"ready\": ") || put_s(&b, (f & 2) ? "true" : "false") || put_s(&b, ",\n      \"gpus\": ")) { Py_XDECREF(labels); goto done; }
+      /* gpus / gpu_breakdown: from the device, or from the bignum table */
+      PyObject* wrec = NULL;
+      if (wide != Py_None && PyDict_Size(wide)) {
+        PyObject* key = PyLong_FromLongLong(node_i);
+        wrec = key ? PyDict_GetItemWithError(wide, key) : NULL; /* borrowed */
+        Py_XDECREF(key);
+        if (!wrec && PyErr_Occurred()) { Py_XDECREF(labels); goto done; }
+      }
+      if (wrec) {
+        PyObject* gp = PyTuple_GetItem(wrec, 0);
+        PyObject* bd = PyTuple_GetItem(wrec, 1);
+        if (!gp || !bd || put_scalar(&b, gp) != 1 || put_s(&b, ",\n      \"gpu_breakdown\": {")) { Py_XDECREF(labels); goto done; }
+        PyObject *k, *v;
+        Py_ssize_t pos = 0, cnt = 0;
+        while (PyDict_Next(bd, &pos, &k, &v)) {
+          if (put_s(&b, cnt++ ? ",\n        " : "\n        ") || put_json_str(&b, k) || put_s(&b, ": ") || put_scalar(&b, v) != 1) { Py_XDECREF(labels); goto done; }
+        }
+        if (put_s(&b, cnt ? "\n      }" : "}")) { Py_XDECREF(labels); goto done; }
+      } else {
+        if (put_i64(&b, gt[i]) || put_s(&b, ",\n      \"gpu_breakdown\": {")) { Py_XDECREF(labels); goto done; }
+        int cnt = 0;
+        for (int k = 0; k < 4; k++)
+          if (f & (8u << k)) {
+            if (put_s(&b, cnt++ ? ",\n        \"" : "\n        \"") || put_s(&b, KEY_NAMES[k]) || put_s(&b, "\": ") || put_i64(&b, gv[4 * i + k])) { Py_XDECREF(labels); goto done; }
+          }
+        if (put_s(&b, cnt ? "\n      }" : "}")) { Py_XDECREF(labels); goto done; }
+      }
+      /* labels */
+      if (put_s(&b, ",\n      \"labels\": {")) { Py_XDECREF(labels); goto done; }
+      {
+        Py_ssize_t cnt = 0;
+        if (labels) {
+          int lt = PyObject_IsTrue(labels);
+          if (lt < 0) { Py_DECREF(labels); goto done; }
+          if (lt) {
+            if (!PyDict_Check(labels)) unsupported = 1;
+            else {
+              PyObject *k, *v;
+              Py_ssize_t pos = 0;
+              while (PyDict_Next(labels, &pos, &k, &v) && !unsupported) {
+                if (!PyUnicode_Check(k)) { unsupported = 1; break; }
+                if (put_s(&b, cnt++ ? ",\n        " : "\n        ") || put_json_str(&b, k) || put_s(&b, ": ")) { Py_DECREF(labels); goto done; }
+                int rc = put_scalar(&b, v);
+                if (rc < 0) { Py_DECREF(labels); goto done; }
+                if (rc == 0) unsupported = 1;
+              }
+            }
+          }
+          Py_DECREF(labels);
+        }
+        if (put_s(&b, cnt ? "\n      }" : "}")) goto done;
+      }
+      /* taints: check-gpu-node.py:208-211 */
+      if (put_s(&b, ",\n      \"taints\": [")) goto done;
+      {
+        Py_ssize_t cnt = 0;
+        PyObject* spec = PyObject_GetAttr(node, s_spec);
+        if (!spec) goto done;
+        int st = PyObject_IsTrue(spec);
+        if (st < 0) { Py_DECREF(spec); goto done; }
+        PyObject* taints = NULL;
+        if (st) {
+          taints = PyObject_GetAttr(spec, s_taints);
+          if (!taints) PyErr_Clear(); /* getattr(node.spec, "taints", None) */
+        }
+        Py_DECREF(spec);
+        if (taints) {
+          int tt = PyObject_IsTrue(taints);
+          if (tt < 0) { Py_DECREF(taints); goto done; }
+          if (tt) {
+            PyObject* it = PyObject_GetIter(taints);
+            if (!it) { Py_DECREF(taints); goto done; }
+            PyObject* t;
+            while ((t = PyIter_Next(it)) && !unsupported) {
+              PyObject* parts[3] = {PyObject_GetAttr(t, s_key), NULL, NULL};
+              parts[1] = parts[0] ? PyObject_GetAttr(t, s_value) : NULL;
+              parts[2] = parts[1] ? PyObject_GetAttr(t, s_effect) : NULL;
+              int bad = !parts[2];
+              static const char* const names[3] = {"\"key\": ", "\"value\": ", "\"effect\": "};
+              if (!bad) bad = put_s(&b, cnt++ ? ",\n        {" : "\n        {");
+              for (int q = 0; q < 3 && !bad && !unsupported; q++) {
+                bad = put_s(&b, q ? ",\n          " : "\n          ") || put_s(&b, names[q]);
+                if (!bad) {
+                  int rc = put_scalar(&b, parts[q]);
+                  if (rc < 0) bad = 1;
+                  if (rc == 0) unsupported = 1;
+                }
+              }
+              if (!bad) bad = put_s(&b, "\n        }");
+              for (int q = 0; q < 3; q++) Py_XDECREF(parts[q]);
+              Py_DECREF(t);
+              if (bad) { Py_DECREF(it); Py_DECREF(taints); goto done; }
+            }
+            Py_DECREF(it);
+            if (PyErr_Occurred()) { Py_DECREF(taints); goto done; }
+          }
+          Py_DECREF(taints);
+        }
+        if (put_s(&b, cnt ? "\n      ]" : "]")) goto done;
+      }
+      if (put_s(&b, "\n    }")) goto done;
+    }
+    if (g && put_s(&b, "\n  ]")) goto done;
+    if (put_s(&b, "\n}")) goto done;
+  }
+  if (unsupported) {
+    result = Py_None;
+    Py_INCREF(result);
+  } else {
+    result = PyUnicode_DecodeUTF8(b.p, (Py_ssize_t)b.n, "surrogatepass");
+  }
+done:
+  free(b.p);
+  Py_XDECREF(seq);
+  PyBuffer_Release(&idx);
+  PyBuffer_Release(&flags);
+  PyBuffer_Release(&totals);
+  PyBuffer_Release(&vals);
+  return result;
+}
+
+static PyMethodDef methods[] = {
+    {"emit_summary_json", emit_summary_json, METH_VARARGS, "the --json document as text"},{"pack_nodes", pack_nodes, METH_VARARGS, "V1Node objects -> (rows bytes, row_ptr bytes, n)"},
                                 {NULL, NULL, 0, NULL}};
 static struct PyModuleDef moddef = {PyModuleDef_HEAD_INIT, "_fastpack", "PNL-v2 packer (C)", -1, methods};
 
@@ -375,5 +618,13 @@ PyMODINIT_FUNC PyInit__fastpack(void) {
   s_conditions = PyUnicode_InternFromString("conditions");
   s_type = PyUnicode_InternFromString("type");
   s_items = PyUnicode_InternFromString("items");
+  s_metadata = PyUnicode_InternFromString("metadata");
+  s_name = PyUnicode_InternFromString("name");
+  s_labels = PyUnicode_InternFromString("labels");
+  s_spec = PyUnicode_InternFromString("spec");
+  s_taints = PyUnicode_InternFromString("taints");
+  s_key = PyUnicode_InternFromString("key");
+  s_value = PyUnicode_InternFromString("value");
+  s_effect = PyUnicode_InternFromString("effect");
   return PyModule_Create(&moddef);
 }
