@@ -143,6 +143,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                "l"(src), "r"(bytes), "r"(smem_addr(bar))
                : "memory");
 }
+// ask for [src, src + bytes) to be brought into L2 (no destination, no completion to wait for)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -648,32 +652,74 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   if (warp == kWalkWarps) {
     // ------------------------------ producer ------------------------------
     if (lane == 0) {
+      // Tickets are taken kAhead tiles before the tile is copied to shared memory, and the tile's
+      // bytes are prefetched into L2 at once: HBM latency is then paid while the stage is still
+      // busy with an earlier tile, and the later bulk copy is an L2 hit.
+      constexpr int kAhead = 2, kQ = kAhead + 1;
+      struct Plan {
+        int tile;  // -1: no more tiles
+        uint32_t lo_al, hi, bytes, cnt;
+        bool direct;
+      } q[kQ];
+      auto plan = [&](Plan& pl) {
+        const uint32_t tile = atomicAdd(&p.scratch->ticket, 1u);
+        if (tile >= p.num_tiles) {
+          pl.tile = -1;
+          return;
+        }
+        const uint32_t first = tile * TN;
+        pl.tile = (int)tile;
+        pl.cnt = min((uint32_t)TN, p.n_nodes - first);
+        const uint32_t lo = __ldg(p.row_ptr + first);
+        pl.hi = __ldg(p.row_ptr + first + pl.cnt);
+        pl.lo_al = lo & ~15u;
+        pl.bytes = ((pl.hi + 15u) & ~15u) - pl.lo_al;
+        pl.direct = pl.hi < lo || pl.hi > p.rows_bytes || pl.bytes > (uint32_t)STAGE_BYTES;
+        if (!pl.direct && pl.bytes) bulk_prefetch_l2(p.rows + pl.lo_al, pl.bytes);
+        bulk_prefetch_l2(p.row_ptr + first, ((pl.cnt + 1) * 4u + 15u) & ~15u);
+      };
+#pragma unroll
+      for (int k = 0; k < kQ; k++) q[k].tile = -1;
+      bool dry = false;
+#pragma unroll
+      for (int k = 0; k < kAhead; k++)
+        if (!dry) {
+          plan(q[k]);
+          dry = q[k].tile < 0;
+        }
       for (uint32_t it = 0;; ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1u;
-        const uint32_t tile = atomicAdd(&p.scratch->ticket, 1u);
-        if (tile >= p.num_tiles) {
-          mbar_wait_parked(&sm.empty[s], ph ^ 1u);
+        // the plan for tile it + kAhead goes into the slot freed by tile it - 1
+        Plan cur;
+#pragma unroll
+        for (int k = 0; k < kQ; k++) {
+          if ((int)(it % kQ) == k) cur = q[k];
+          if ((int)((it + kAhead) % kQ) == k) {
+            if (!dry) {
+              plan(q[k]);
+              dry = q[k].tile < 0;
+            } else {
+              q[k].tile = -1;
+            }
+          }
+        }
+        mbar_wait_parked(&sm.empty[s], ph ^ 1u);
+        if (cur.tile < 0) {
           sm.tile[s] = -1;
           mbar_arrive(&sm.full[s]);
           break;
         }
-        const uint32_t first = tile * TN;
-        const uint32_t cnt = min((uint32_t)TN, p.n_nodes - first);
-        const uint32_t lo = __ldg(p.row_ptr + first), hi = __ldg(p.row_ptr + first + cnt);
-        const uint32_t lo_al = lo & ~15u;
-        const uint32_t bytes = ((hi + 15u) & ~15u) - lo_al;
-        const uint32_t rp_bytes = ((cnt + 1) * 4u + 15u) & ~15u;
-        const bool direct = hi < lo || hi > p.rows_bytes || bytes > (uint32_t)STAGE_BYTES;
-        mbar_wait_parked(&sm.empty[s], ph ^ 1u);
-        sm.tile[s] = (int)tile;
-        sm.lo[s] = lo_al;
-        sm.hi[s] = direct ? (uint32_t)min(p.rows_bytes, (uint64_t)0xFFFFFFFFu) : hi;
-        sm.direct[s] = direct ? 1u : 0u;
-        const uint32_t stage_bytes = direct ? 0u : bytes;
+        const uint32_t first = (uint32_t)cur.tile * TN;
+        const uint32_t rp_bytes = ((cur.cnt + 1) * 4u + 15u) & ~15u;
+        sm.tile[s] = cur.tile;
+        sm.lo[s] = cur.lo_al;
+        sm.hi[s] = cur.direct ? (uint32_t)min(p.rows_bytes, (uint64_t)0xFFFFFFFFu) : cur.hi;
+        sm.direct[s] = cur.direct ? 1u : 0u;
+        const uint32_t stage_bytes = cur.direct ? 0u : cur.bytes;
         mbar_arrive_expect_tx(&sm.full[s], rp_bytes + stage_bytes);
         bulk_g2s(sm.rp[s], p.row_ptr + first, rp_bytes, &sm.full[s]);
-        if (stage_bytes) bulk_g2s(sm.stage[s], p.rows + lo_al, stage_bytes, &sm.full[s]);
+        if (stage_bytes) bulk_g2s(sm.stage[s], p.rows + cur.lo_al, stage_bytes, &sm.full[s]);
       }
     }
     __syncwarp();  // lanes 1..31 rejoin lane 0 before the CTA-wide barrier below
