@@ -189,6 +189,16 @@ def run_b200(args):
         nccl_id = box[0]
     clf = engine.Classifier(local, rank, world, nccl_id)
     clf.reserve(n)
+    gather_kind = "none"
+    if world > 1:
+        gather_kind = "nccl"
+        if args.gather == "fused":
+            try:
+                clf.fleet_enable(n_total)
+                gather_kind = "fused"
+            except Exception as e:          # peer mapping unavailable: the NCCL gather stays in place
+                if rank == 0:
+                    print(f"fused gather unavailable ({e}); using NCCL", file=sys.stderr)
     out = engine.DeviceResult.alloc(n, dev)
     # the gather target holds the fleet-wide ordered index list and counts (north star: all-reduce of the
     # counts + all-gather-v of the compacted indices); per-node values stay on the rank that owns them
@@ -291,7 +301,10 @@ def run_b200(args):
         "config": {"workload": WORKLOAD, "nodes": n_total, "nodes_per_rank": n, "rows_bytes_per_rank": int(total),
                    "gpu_nodes": g_fleet, "ready_gpu_nodes": int(counts[1]), "parallelism": f"shard{world}",
                    "cache": "inputs (rows_bytes_per_rank) exceed the 126 MB L2; no flush needed",
-                   "collectives": "none" if world == 1 else "one ncclAllGather of per-rank (counts block + compacted indices) slots, then an unpack kernel"},
+                   "collectives": {"none": "none",
+                                   "nccl": "one ncclAllGather of per-rank (counts block + compacted indices) slots, then an unpack kernel",
+                                   "fused": "none after the kernel: classify stores indices and counts into every rank's buffer over NVLink "
+                                            "(peer stores), gather = flag wait + local unpack"}[gather_kind]},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": peak_src, "kernel": "gnc::classify_kernel",
                      "kernel_ms": kern_mean, "algorithmic_bytes_per_launch": int(algo_bytes),
@@ -311,6 +324,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nodes", type=int, default=FLEET_NODES)
+    ap.add_argument("--gather", default="fused", choices=["fused", "nccl"], help="multi-GPU combine step")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-sample", type=int, default=2_000_000, help="nodes the 1-core CPU baseline classifies (0 = skip)")
     args = ap.parse_args()

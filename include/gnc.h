@@ -116,6 +116,15 @@ int gnc_classify(gnc_ctx*, const gnc_batch* in, const gnc_result* out, void* cud
  * rank's gnc_classify result; `all` must hold the fleet-wide GPU-node count. */
 int gnc_gather(gnc_ctx*, const gnc_result* local, const gnc_result* all, void* cuda_stream);
 
+/* Multi-GPU only, optional, collective (every rank calls it once, after gnc_create): switch the
+ * context to the fused gather.  Afterwards gnc_classify also stores each GPU node's index and, at the
+ * end, the counts block straight into every rank's buffer over NVLink while the kernel runs, and
+ * gnc_gather (indices + counts form) only waits for the other ranks' flags and packs locally -- no
+ * collective follows the kernel.  `fleet_nodes_cap` bounds the fleet's node count.  Ranks must call
+ * gnc_classify and gnc_gather in step (the same number of times); up to 8 ranks on one NVLink domain.
+ * Returns an error (and leaves the NCCL path in place) where peer mapping is not available. */
+int gnc_fleet_enable(gnc_ctx*, uint32_t fleet_nodes_cap, void* cuda_stream);
+
 /* Same classification from HOST memory: copies the shard to the device in pipelined chunks,
  * classifies, and copies flags / GPU-node records / counts back to the caller's HOST buffers
  * (the gnc_batch / gnc_result pointers are host pointers here).  Blocks until the results are in

@@ -52,6 +52,24 @@ constexpr uint32_t kEpochMask = (1u << 22) - 1;
 constexpr int kLookbackSpan = 16;                   // tiles per lane per round
 constexpr int kLookbackWindow = 32 * kLookbackSpan; // tiles per round
 
+constexpr int kFleetMaxWorld = 8;
+constexpr uint32_t kFleetHeader = 2 * GNC_N_COUNTS;  // a slot starts with the rank's counts block (16 x i64)
+constexpr unsigned long long kFleetTimeoutNs = 2000000000ull;
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned long long ld_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 struct Params {
   const uint8_t* rows;
   const uint32_t* row_ptr;
@@ -73,6 +91,17 @@ struct Params {
   unsigned long long* inc;  // [tiles rounded up to the look-back window]
   uint32_t* agg;            // likewise
   unsigned long long* trace;  // debug builds only (GNC_TRACE): [cta][iteration][8] timestamps
+  // Fused gather (multi-GPU, gnc_fleet_enable): every GPU node's index is also stored straight into
+  // every rank's fleet buffer over NVLink while the kernel runs, so that no collective follows it.
+  uint32_t fleet_world;                      // 0: off
+  uint32_t fleet_rank;
+  uint32_t fleet_cap;                        // indices per slot
+  uint32_t fleet_slot_u32;                   // u32 per slot: kFleetHeader + fleet_cap
+  unsigned long long fleet_epoch;            // this launch's number
+  unsigned long long fleet_ack_need;         // every peer must have consumed this epoch before its slots are rewritten
+  uint32_t* fleet_peer[kFleetMaxWorld];      // peer-mapped slots [world][fleet_slot_u32] of this epoch's parity, per rank
+  unsigned long long* fleet_flag[kFleetMaxWorld];  // peer-mapped arrival flags [world] of this parity, per rank
+  const unsigned long long* fleet_ack;       // local: [world] epochs each peer has consumed
 };
 
 __constant__ uint32_t c_nd_runs[GNC_ND_RUNS] = {GNC_ND_RUN_LIST};
@@ -647,6 +676,15 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   }
   if (tid < GNC_N_COUNTS) sm.acc[tid] = 0;
   if (tid < kRing) sm.tile_cnt[tid] = 0;
+  if (p.fleet_world && tid < (int)p.fleet_world && p.fleet_ack_need) {
+    // the slots about to be rewritten were last filled two launches ago: every peer must have read them
+    const unsigned long long t0 = global_ns();
+    while (ld_sys_u64(p.fleet_ack + tid) < p.fleet_ack_need)
+      if (global_ns() - t0 > kFleetTimeoutNs) {
+        atomicAdd(&sm.acc[GNC_C_OUT_DROPPED], 1ull << 40);  // poisons the counts: the host reports it
+        break;
+      }
+  }
   __syncthreads();
 
   if (warp == kWalkWarps) {
@@ -790,6 +828,10 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
             v0 = (short)(sv.x & 0xFFFFu), v1 = (short)(sv.x >> 16), v2 = (short)(sv.y & 0xFFFFu), v3 = (short)(sv.y >> 16);
           }
           p.gpu_idx[pos] = p.node_base + first_e + j;
+          if (p.fleet_world && pos < p.fleet_cap) {
+            const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + pos;
+            for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][at] = p.node_base + first_e + j;
+          }
           p.gpu_total[pos] = v0 + v1 + v2 + v3;
           longlong2* vo = reinterpret_cast<longlong2*>(p.gpu_vals + 4ull * pos);
           vo[0] = make_longlong2(v0, v1);
@@ -930,7 +972,8 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         atomicAdd(&sc->accum[c], sm.acc[c]);
       }
     }
-    __threadfence();
+    if (p.fleet_world) __threadfence_system();  // this CTA's peer stores are out before it counts as done
+    else __threadfence();
     const uint32_t prev = atomicAdd(&sc->done, 1u);
     if (prev == gridDim.x - 1) {  // last CTA: publish the counts block and re-arm the scratch
       __threadfence();
@@ -939,6 +982,13 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         if (c == GNC_C_SCANNED) v = p.n_nodes;
         p.counts[c] = v;
         sc->accum[c] = 0;
+        if (p.fleet_world)
+          for (uint32_t q = 0; q < p.fleet_world; q++)
+            reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[c] = v;
+      }
+      if (p.fleet_world) {  // every index and the counts are on their way: raise this rank's flag everywhere
+        __threadfence_system();
+        for (uint32_t q = 0; q < p.fleet_world; q++) st_sys_u64(p.fleet_flag[q] + p.fleet_rank, p.fleet_epoch);
       }
       sc->ticket = 0;
       sc->defer_count = 0;

@@ -85,6 +85,14 @@ struct gnc_ctx {
   void* comm = nullptr;
   int64_t* d_all_counts = nullptr;  // [world][GNC_N_COUNTS]
   int64_t* h_all_counts = nullptr;  // pinned
+  struct Fleet {                    // fused gather (gnc_fleet_enable)
+    bool on = false;
+    uint32_t cap = 0, slot_u32 = 0;
+    size_t region_bytes = 0, bytes = 0;
+    char* base[gnc::kFleetMaxWorld] = {};  // every rank's fleet buffer as mapped here (own: local allocation)
+    unsigned long long epoch = 0;
+    unsigned int* unpack_done = nullptr;
+  } fleet;
   void* json_scratch = nullptr;     // gnc_json_to_pnl working arrays
   size_t json_scratch_bytes = 0;
   uint32_t* gather_buf = nullptr;   // [world][32 + gather_cap] u32: counts block + indices of every rank
@@ -155,6 +163,102 @@ int check_batch(gnc_ctx* c, const gnc_batch* in, const gnc_result* out) {
   return GNC_OK;
 }
 
+// ---- fused gather: per-launch addresses inside every rank's fleet buffer -------------------------
+// buffer layout: [parity 0: world slots][parity 1: world slots][flags: 2 x world u64][acks: world u64]
+void fleet_params(gnc_ctx* c, Params* p) {
+  gnc_ctx::Fleet& f = c->fleet;
+  const unsigned long long e = ++f.epoch;
+  const size_t parity = e & 1;
+  p->fleet_world = (uint32_t)c->world;
+  p->fleet_rank = (uint32_t)c->rank;
+  p->fleet_cap = f.cap;
+  p->fleet_slot_u32 = f.slot_u32;
+  p->fleet_epoch = e;
+  p->fleet_ack_need = e >= 3 ? e - 2 : 0;
+  for (int q = 0; q < c->world; q++) {
+    p->fleet_peer[q] = (uint32_t*)(f.base[q] + parity * f.region_bytes);
+    p->fleet_flag[q] = (unsigned long long*)(f.base[q] + 2 * f.region_bytes) + parity * c->world;
+  }
+  p->fleet_ack = (const unsigned long long*)(f.base[c->rank] + 2 * f.region_bytes + 2 * (size_t)c->world * 8);
+}
+
+__global__ void fleet_publish_empty_kernel(const Params p) {
+  if (threadIdx.x == 0) {
+    for (uint32_t q = 0; q < p.fleet_world; q++)
+      for (int s = 0; s < GNC_N_COUNTS; s++)
+        reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[s] = 0;
+    __threadfence_system();
+    for (uint32_t q = 0; q < p.fleet_world; q++) gnc::st_sys_u64(p.fleet_flag[q] + p.fleet_rank, p.fleet_epoch);
+  }
+}
+
+struct AckPtrs {
+  unsigned long long* p[gnc::kFleetMaxWorld];
+};
+
+// Wait until every rank's slot of this epoch has arrived in the LOCAL fleet buffer, then build the dense
+// rank-ordered index list and the summed counts, then tell every rank that its slot here was consumed.
+__global__ void fleet_unpack_kernel(const uint32_t* slots, const unsigned long long* flags, unsigned long long epoch, int world, int rank,
+                                    uint32_t slot_u32, uint32_t cap, uint32_t* out_idx, uint32_t out_cap, int64_t* out_counts,
+                                    unsigned int* done, AckPtrs ack_peer) {
+  __shared__ unsigned long long off[gnc::kFleetMaxWorld + 1];
+  __shared__ int timed_out;
+  if (threadIdx.x == 0) timed_out = 0;
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const unsigned long long t0 = gnc::global_ns();
+    while (gnc::ld_sys_u64(flags + threadIdx.x) < epoch)
+      if (gnc::global_ns() - t0 > gnc::kFleetTimeoutNs) {
+        timed_out = 1;
+        break;
+      }
+  }
+  __syncthreads();
+  __threadfence_system();
+  if (threadIdx.x == 0) {
+    off[0] = 0;
+    for (int r = 0; r < world; r++) off[r + 1] = off[r] + (unsigned long long)reinterpret_cast<const long long*>(slots + (size_t)r * slot_u32)[GNC_C_GPU_NODES];
+  }
+  __syncthreads();
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x, t0 = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  for (int r = 0; r < world; r++) {
+    const uint32_t* src = slots + (size_t)r * slot_u32 + gnc::kFleetHeader;
+    const unsigned long long cnt = min(off[r + 1] - off[r], (unsigned long long)cap);
+    for (unsigned long long i = t0; i < cnt; i += stride)
+      if (off[r] + i < out_cap) out_idx[off[r] + i] = __ldcv(src + i);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    long long sum[GNC_N_COUNTS];
+    unsigned __int128 key[4] = {0, 0, 0, 0};
+    unsigned long long lost = 0;
+    for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] = 0;
+    for (int r = 0; r < world; r++) {
+      const long long* cr = reinterpret_cast<const long long*>(slots + (size_t)r * slot_u32);
+      for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] += cr[s];
+      for (int k = 0; k < 4; k++)
+        key[k] += ((unsigned __int128)(unsigned long long)cr[GNC_C_KEY_HI + k] << 64) | (unsigned long long)cr[GNC_C_KEY_LO + k];
+      const unsigned long long cnt = off[r + 1] - off[r];
+      if (cnt > cap) lost += cnt - cap;
+    }
+    if (off[world] > out_cap) lost = max(lost, off[world] - out_cap);
+    for (int k = 0; k < 4; k++) {
+      sum[GNC_C_KEY_LO + k] = (long long)(unsigned long long)key[k];
+      sum[GNC_C_KEY_HI + k] = (long long)(unsigned long long)(key[k] >> 64);
+    }
+    sum[GNC_C_OUT_DROPPED] += (long long)lost + (timed_out ? (1ll << 41) : 0);
+    for (int s = 0; s < GNC_N_COUNTS; s++) out_counts[s] = sum[s];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(done, 1u) == gridDim.x - 1) {  // every block has read the slots: peers may overwrite them
+      *done = 0;
+      __threadfence_system();
+      for (int q = 0; q < world; q++) gnc::st_sys_u64(ack_peer.p[q] + rank, epoch);
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -218,6 +322,13 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
   CUDA_TRY(c, cudaSetDevice(c->device));
   if (in->n_nodes == 0) {
     CUDA_TRY(c, cudaMemsetAsync(out->counts, 0, GNC_N_COUNTS * sizeof(int64_t), stream));
+    if (c->fleet.on) {  // an empty shard still has to tell the other ranks so
+      Params p = {};
+      fleet_params(c, &p);
+      fleet_publish_empty_kernel<<<1, 32, 0, stream>>>(p);
+      CUDA_TRY(c, cudaGetLastError());
+      c->launches++;
+    }
     return GNC_OK;
   }
   const int v = pick_variant(c, in->rows_bytes, in->n_nodes);
@@ -231,7 +342,7 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
                                 c->scratch_tiles * (sizeof(unsigned long long) + sizeof(uint32_t)), stream));
     c->epoch = 1;
   }
-  Params p;
+  Params p = {};
   p.rows = in->rows;
   p.row_ptr = in->row_ptr;
   p.rows_bytes = in->rows_bytes;
@@ -255,6 +366,7 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
 #ifdef GNC_TRACE
   p.trace = c->trace;
 #endif
+  if (c->fleet.on) fleet_params(c, &p);
   const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(c->sm_count * c->ctas_per_sm[v]));
   var.launch(p, grid, var.smem, stream);
   CUDA_TRY(c, cudaGetLastError());
@@ -481,7 +593,7 @@ struct NcclApi {
   void* lib = nullptr;
   std::string err;
 };
-constexpr int kNcclUint32 = 3, kNcclInt64 = 4;
+constexpr int kNcclUint8 = 1, kNcclUint32 = 3, kNcclInt64 = 4;
 
 NcclApi* nccl_api() {
   static NcclApi api;
@@ -530,6 +642,12 @@ int comm_init(gnc_ctx* c, const void* id, size_t id_len) {
 }
 
 void comm_destroy(gnc_ctx* c) {
+  if (c->fleet.on) {
+    for (int q = 0; q < c->world; q++)
+      if (q != c->rank && c->fleet.base[q]) cudaIpcCloseMemHandle(c->fleet.base[q]);
+    cudaFree(c->fleet.base[c->rank]);
+    c->fleet.on = false;
+  }
   if (c->comm) nccl_api()->CommDestroy(c->comm);
   c->comm = nullptr;
   cudaFree(c->d_all_counts);
@@ -602,6 +720,59 @@ extern "C" int gnc_comm_id(void* id, size_t cap, size_t* len) {
   return GNC_OK;
 }
 
+extern "C" int gnc_fleet_enable(gnc_ctx* c, uint32_t fleet_nodes_cap, void* cuda_stream) {
+  if (!c) return GNC_ERR_ARG;
+  if (c->world == 1) return GNC_OK;
+  if (c->world > gnc::kFleetMaxWorld) return fail(c, GNC_ERR_ARG, "the fused gather supports up to 8 ranks");
+  if (!c->comm) return fail(c, GNC_ERR_STATE, "context has no communicator");
+  if (c->fleet.on) return fail(c, GNC_ERR_STATE, "the fused gather is already enabled");
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  NcclApi* n = nccl_api();
+  gnc_ctx::Fleet& f = c->fleet;
+  f.cap = (uint32_t)((((size_t)fleet_nodes_cap + c->world - 1) / c->world + 3) & ~(size_t)3);
+  f.slot_u32 = gnc::kFleetHeader + f.cap;
+  f.region_bytes = ((size_t)c->world * f.slot_u32 * 4 + 255) & ~(size_t)255;
+  f.bytes = 2 * f.region_bytes + 3 * (size_t)c->world * 8 + 256;
+  char* local = nullptr;
+  CUDA_TRY(c, cudaMalloc((void**)&local, f.bytes));
+  CUDA_TRY(c, cudaMemset(local, 0, f.bytes));
+  cudaIpcMemHandle_t mine;
+  CUDA_TRY(c, cudaIpcGetMemHandle(&mine, local));
+  // every rank's handle to every rank (through the communicator that already exists)
+  char* d_handles = nullptr;
+  std::vector<cudaIpcMemHandle_t> all(c->world);
+  CUDA_TRY(c, cudaMalloc((void**)&d_handles, sizeof(mine) * c->world));
+  CUDA_TRY(c, cudaMemcpyAsync(d_handles + sizeof(mine) * c->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, stream));
+  NCCL_TRY(c, n->AllGather(d_handles + sizeof(mine) * c->rank, d_handles, sizeof(mine), kNcclUint8, c->comm, stream));
+  CUDA_TRY(c, cudaMemcpyAsync(all.data(), d_handles, sizeof(mine) * c->world, cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(c, cudaStreamSynchronize(stream));
+  for (int q = 0; q < c->world; q++) {
+    if (q == c->rank) {
+      f.base[q] = local;
+    } else {
+      void* ptr = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        for (int k = 0; k < q; k++)
+          if (k != c->rank) cudaIpcCloseMemHandle(f.base[k]);
+        cudaFree(local);
+        cudaFree(d_handles);
+        return fail(c, GNC_ERR_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+      }
+      f.base[q] = (char*)ptr;
+    }
+  }
+  // nobody writes into a peer before every peer has zeroed its buffer: one more trip round the ranks
+  NCCL_TRY(c, n->AllGather(d_handles + sizeof(mine) * c->rank, d_handles, sizeof(mine), kNcclUint8, c->comm, stream));
+  CUDA_TRY(c, cudaStreamSynchronize(stream));
+  CUDA_TRY(c, cudaFree(d_handles));
+  f.unpack_done = (unsigned int*)(local + f.bytes - 256);
+  f.epoch = 0;
+  f.on = true;
+  return GNC_OK;
+}
+
 extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result* all, void* cuda_stream) {
   if (!c) return GNC_ERR_ARG;
   if (!local || !all || !local->counts || !all->counts) return fail(c, GNC_ERR_ARG, "null result or counts");
@@ -614,6 +785,23 @@ extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result*
   }
   if (!c->comm) return fail(c, GNC_ERR_STATE, "context has no communicator");
   NcclApi* n = nccl_api();
+  if (c->fleet.on && c->fleet.epoch && !all->gpu_total && !all->gpu_vals) {
+    // Fused gather: the classify kernel already stored this rank's indices and counts into every
+    // rank's fleet buffer over NVLink.  What is left is local: wait for the other ranks' flags, pack
+    // the slots into the dense rank-ordered list, add the counts up, acknowledge.  No collective.
+    if (!all->gpu_idx) return fail(c, GNC_ERR_ARG, "gpu_idx is null");
+    gnc_ctx::Fleet& f = c->fleet;
+    const size_t parity = f.epoch & 1;
+    AckPtrs ap = {};
+    for (int q = 0; q < c->world; q++) ap.p[q] = (unsigned long long*)(f.base[q] + 2 * f.region_bytes + 2 * (size_t)c->world * 8);
+    fleet_unpack_kernel<<<2 * c->sm_count, 256, 0, stream>>>(
+        (const uint32_t*)(f.base[c->rank] + parity * f.region_bytes),
+        (const unsigned long long*)(f.base[c->rank] + 2 * f.region_bytes) + parity * c->world, f.epoch, c->world, c->rank, f.slot_u32,
+        f.cap, all->gpu_idx, all->out_cap, all->counts, f.unpack_done, ap);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches += 1;
+    return GNC_OK;
+  }
   if (!all->gpu_total && !all->gpu_vals) {
     // Indices and counts only (the north star's gather): ONE in-place all-gather of fixed-size slots
     // -- each rank's counts block followed by its indices -- then a kernel that packs the slots into
@@ -785,7 +973,7 @@ extern "C" int gnc_classify_static(int device, const gnc_batch* in, const gnc_re
     STATIC_CUDA_TRY(cudaMemsetAsync((char*)st.scratch + sizeof(ScratchHeader), 0, kStaticScratchBytes - sizeof(ScratchHeader), stream));
     st.epoch = 1;
   }
-  Params p;
+  Params p = {};
   p.rows = in->rows;
   p.row_ptr = in->row_ptr;
   p.rows_bytes = in->rows_bytes;

@@ -174,6 +174,11 @@ class Classifier:
         self._check(self.lib.gnc_classify(self._h, ctypes.byref(b), ctypes.byref(r), ctypes.c_void_p(s.cuda_stream)))
         return out
 
+    def fleet_enable(self, fleet_nodes_cap: int, stream: Optional[torch.cuda.Stream] = None):
+        """Collective: switch to the fused gather (classify stores indices into every rank over NVLink)."""
+        s = stream or torch.cuda.current_stream(self.device)
+        self._check(self.lib.gnc_fleet_enable(self._h, fleet_nodes_cap, ctypes.c_void_p(s.cuda_stream)))
+
     def gather(self, local: DeviceResult, fleet: DeviceResult, stream: Optional[torch.cuda.Stream] = None) -> DeviceResult:
         s = stream or torch.cuda.current_stream(self.device)
         a, b = local.c_struct(), fleet.c_struct()

@@ -46,6 +46,17 @@ def _worker(rank, world, port, n, out_dir):
     torch.cuda.synchronize()
     assert torch.equal(lean.counts, fleet.counts)
     assert torch.equal(lean.gpu_idx[:int(lean.counts[0])], fleet.gpu_idx[:int(fleet.counts[0])])
+    # the fused gather: classify itself stores the indices into every rank over NVLink; run it for several
+    # epochs so that both buffer parities are reused and the acknowledgements are exercised
+    clf.fleet_enable(n)
+    fused = engine.DeviceResult.alloc(n, dev, defer_cap=1, records=False)
+    for _ in range(5):
+        fused.gpu_idx.fill_(-1)
+        clf.classify(engine.DeviceBatch.from_packed(p, dev, node_base=lo), local)
+        clf.gather(local, fused)
+        torch.cuda.synchronize()
+        assert torch.equal(fused.counts, fleet.counts), (fused.counts, fleet.counts)
+        assert torch.equal(fused.gpu_idx[:int(fused.counts[0])], fleet.gpu_idx[:int(fleet.counts[0])])
     counts = fleet.counts.cpu().numpy()
     g = int(counts[0])
     np.save(os.path.join(out_dir, f"c{rank}.npy"), counts)
