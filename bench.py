@@ -27,6 +27,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLEET_NODES = 10_000_000
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE classify launch on the default workload (N=1), from the
+# `ncu --set full` capture summarised in profiles/r01_ncu_classify_10m.txt (2.1584 GB read + 0.2987 GB written)
+NCU_TRAFFIC_BYTES_DEFAULT_WORKLOAD = 2_457_097_472
 METRIC = "node_records_per_sec"
 UNIT = "nodes/s"
 WORKLOAD = "g1-10M-node synthetic NodeList (BASELINE.json configs[2]; seed 0)"
@@ -306,7 +309,8 @@ def run_b200(args):
                                    "fused": "none after the kernel: classify stores indices and counts into every rank's buffer over NVLink "
                                             "(peer stores), gather = flag wait + local unpack"}[gather_kind]},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "gnc::classify_kernel",
+                     "traffic": NCU_TRAFFIC_BYTES_DEFAULT_WORKLOAD if (world == 1 and n_total == FLEET_NODES) else None,
+                     "traffic_source": "profiles/r01_ncu_classify_10m.txt (ncu --set full, one launch)", "peak_source": peak_src, "kernel": "gnc::classify_kernel",
                      "kernel_ms": kern_mean, "algorithmic_bytes_per_launch": int(algo_bytes),
                      "bytes_per_node": algo_bytes / n, "frac_of_8TBps": achieved / 8000.0},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
