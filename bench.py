@@ -161,9 +161,15 @@ def run_b200(args):
     import torch.distributed as dist
     from oracle import ensure_kubernetes_importable
     ensure_kubernetes_importable()
-    from k8s_gpu_node_checker_b200 import engine, synth
+    from k8s_gpu_node_checker_b200 import engine, native, synth
 
     rank = int(os.environ.get("RANK", "0"))
+    if not os.path.exists(native.LIB_PATH):      # normally built by __graft_entry__.build(); there is no CPU fallback
+        if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+            native.build()
+        else:
+            while not os.path.exists(native.LIB_PATH):
+                time.sleep(0.5)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus:

@@ -28,6 +28,16 @@ def pytest_collection_modifyitems(config, items):
             it.add_marker(skip)
 
 
+@pytest.fixture(scope="session", autouse=True)
+def native_pieces_built():
+    """Build what is missing (nvcc and gcc are in the image on both machines); never silently skip."""
+    from k8s_gpu_node_checker_b200 import native, pnl
+    if not os.path.exists(native.LIB_PATH):
+        native.build()
+    if pnl._fastpack() is None:
+        native.build_fastpack()
+
+
 @pytest.fixture(scope="session")
 def golden():
     import json
