@@ -1,12 +1,16 @@
 // classify.cuh -- the node-classification kernel (sm_100a).
 //
-// Persistent CTAs, four warp roles.  A producer warp takes tile tickets in fleet order and stages each
-// tile's bytes in shared memory with TMA bulk copies (cp.async.bulk + mbarrier).  TN "capacity"
-// threads and TN "condition" threads each walk one node's row out of shared memory.  GPU nodes are
-// compacted in fleet order: warp ballots give ranks, two scan warps turn per-warp counts into output
-// positions with a 512-tile-wide decoupled look-back over global descriptors, and the capacity
-// threads write a tile's records one iteration later (from a thread-private stash), so no walker
-// ever waits for a global-memory round trip.
+// Persistent CTAs (two per SM), three warp roles, no CTA-wide barrier in the loop:
+//   producer  takes tile tickets in fleet order two tiles ahead, prefetches each tile into L2
+//             (cp.async.bulk.prefetch.L2) and later stages it in shared memory with TMA bulk copies
+//             (cp.async.bulk + mbarrier complete_tx);
+//   walkers   one thread per node: scan the row's length table without a branch per entry, look at
+//             the text of the few candidate entries, publish flags / ranks / partial counts, and
+//             write the tile's GPU-node records kRing-1 iterations later from a private stash;
+//   scan      two warps turn per-warp counts into output positions with a 512-tile-wide decoupled
+//             look-back over global descriptors and fold the tile's counts into registers.
+// GPU nodes come out in fleet order (ballot ranks + prefix, no atomics decide positions).  With the
+// fused gather enabled each index is also stored into every other rank's buffer over NVLink.
 //
 // Reference behaviour implemented (file:line in /root/reference/check-gpu-node.py):
 //   key match + quantity parse  :186-195      Ready test  :172-178      gpus sum / filter  :201, :222-225
@@ -137,21 +141,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
   } while (!ok);
 }
-// same, for waits expected to last microseconds: sleep between polls so the issue slots go to walkers
-__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
-  uint32_t addr = smem_addr(bar), ok;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (ok) break;
-    __nanosleep(200);
-  }
-}
 // for warps with nothing else to do: let the hardware park the thread for up to ~1 us per try
 __device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
   uint32_t addr = smem_addr(bar), ok;
@@ -208,18 +197,6 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* buf, uint32_t off) {
 __host__ __device__ constexpr uint32_t pack4(const char* s, int i, int n) {
   return (i < n ? (uint32_t)(uint8_t)s[i] : 0u) | (i + 1 < n ? (uint32_t)(uint8_t)s[i + 1] << 8 : 0u) |
          (i + 2 < n ? (uint32_t)(uint8_t)s[i + 2] << 16 : 0u) | (i + 3 < n ? (uint32_t)(uint8_t)s[i + 3] << 24 : 0u);
-}
-__host__ __device__ constexpr uint32_t mask4(int i, int n) {
-  return (i < n ? 0xFFu : 0u) | (i + 1 < n ? 0xFF00u : 0u) | (i + 2 < n ? 0xFF0000u : 0u) | (i + 3 < n ? 0xFF000000u : 0u);
-}
-
-// bytes [2, N) of the key at `kp` against literal S (bytes 0..1 were checked from the entry header)
-template <int N>
-__device__ __forceinline__ bool key_tail_eq(const uint8_t* buf, uint32_t kp, const char (&S)[N + 1]) {
-  bool eq = true;
-#pragma unroll
-  for (int i = 2; i < N; i += 4) eq = eq && ((ld32u(buf, kp + i) & mask4(i, N)) == pack4(S, i, N));
-  return eq;
 }
 
 // ------------------------------------------------------------------------------------------------
