@@ -451,6 +451,14 @@ extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_resu
   if (in->n_nodes == 0) return GNC_OK;
   if (!in->rows || !in->row_ptr || !out->flags || !out->gpu_idx || !out->gpu_total || !out->gpu_vals)
     return fail(c, GNC_ERR_ARG, "null host buffer");
+  // The chunks below are classified on their own: the fused gather (one epoch per fleet-wide step)
+  // stays out of it.
+  struct FleetPause {
+    gnc_ctx* c;
+    bool was;
+    explicit FleetPause(gnc_ctx* ctx) : c(ctx), was(ctx->fleet.on) { c->fleet.on = false; }
+    ~FleetPause() { c->fleet.on = was; }
+  } fleet_pause(c);
   // Chunks of ~1M nodes: chunk k+1's upload overlaps chunk k's kernel and download.
   const uint32_t kChunk = 1u << 20;
   const uint32_t n = in->n_nodes;
