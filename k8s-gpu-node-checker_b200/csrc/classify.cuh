@@ -165,6 +165,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -611,8 +614,6 @@ struct Smem {
   alignas(128) uint8_t stage[STAGES][STAGE_BYTES + 32];
   alignas(16) uint32_t rp[STAGES][TN + 8];
   alignas(8) uint64_t full[STAGES];  // producer/TMA -> walkers: the stage holds a tile
-  uint64_t empty[STAGES];            // walkers -> producer: every walker warp is done with the stage
-  uint64_t cnt_full[kRing];          // walkers -> scan warp: per-warp partial counts of a tile are in part[]
   uint64_t pref_full[kRing];         // scan warp -> walkers: output positions are in warp_base[]
   unsigned long long acc[GNC_N_COUNTS];
   int tile[STAGES];
@@ -637,16 +638,20 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   S& sm = *reinterpret_cast<S*>(smem_raw);
   constexpr int kWalkWarps = TN / 32;
   static_assert(TN % 32 == 0 && kWalkWarps <= 32 && TN < 1024, "one scan-warp lane per walker warp; 10-bit tile counts");
+  // Hand-offs to warps that would otherwise do nothing but poll use hardware named barriers (the
+  // waiting warp is descheduled, it issues nothing): stage s free -> producer, counts of ring slot b
+  // ready -> the scan warp that owns slot b.  Both have TN walker threads arriving and one warp waiting.
+  static_assert(kRing % 2 == 0, "ring slot b always belongs to scan warp b & 1");
+  constexpr int kBarStage = 1, kBarCnt = 1 + STAGES, kBarThreads = TN + 32;
+  static_assert(kBarCnt + kRing <= 16, "named barrier ids");
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; s++) {
       mbar_init(&sm.full[s], 1);
-      mbar_init(&sm.empty[s], kWalkWarps);
     }
     for (int b = 0; b < kRing; b++) {
-      mbar_init(&sm.cnt_full[b], kWalkWarps);
       mbar_init(&sm.pref_full[b], 1);
     }
     mbar_init_fence();
@@ -666,7 +671,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
 
   if (warp == kWalkWarps) {
     // ------------------------------ producer ------------------------------
-    if (lane == 0) {
+    {
       // Tickets are taken kAhead tiles before the tile is copied to shared memory, and the tile's
       // bytes are prefetched into L2 at once: HBM latency is then paid while the stage is still
       // busy with an earlier tile, and the later bulk copy is an L2 hit.
@@ -696,35 +701,44 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
 #pragma unroll
       for (int k = 0; k < kQ; k++) q[k].tile = -1;
       bool dry = false;
+      if (lane == 0) {
 #pragma unroll
-      for (int k = 0; k < kAhead; k++)
-        if (!dry) {
-          plan(q[k]);
-          dry = q[k].tile < 0;
-        }
+        for (int k = 0; k < kAhead; k++)
+          if (!dry) {
+            plan(q[k]);
+            dry = q[k].tile < 0;
+          }
+      }
+      // lane 0 does the work; the whole warp waits at the named barrier, so the loop is warp-uniform
       for (uint32_t it = 0;; ++it) {
         const int s = it % STAGES;
-        const uint32_t ph = (it / STAGES) & 1u;
         // the plan for tile it + kAhead goes into the slot freed by tile it - 1
         Plan cur;
+        cur.tile = -1;
+        if (lane == 0) {
 #pragma unroll
-        for (int k = 0; k < kQ; k++) {
-          if ((int)(it % kQ) == k) cur = q[k];
-          if ((int)((it + kAhead) % kQ) == k) {
-            if (!dry) {
-              plan(q[k]);
-              dry = q[k].tile < 0;
-            } else {
-              q[k].tile = -1;
+          for (int k = 0; k < kQ; k++) {
+            if ((int)(it % kQ) == k) cur = q[k];
+            if ((int)((it + kAhead) % kQ) == k) {
+              if (!dry) {
+                plan(q[k]);
+                dry = q[k].tile < 0;
+              } else {
+                q[k].tile = -1;
+              }
             }
           }
         }
-        mbar_wait_parked(&sm.empty[s], ph ^ 1u);
-        if (cur.tile < 0) {
-          sm.tile[s] = -1;
-          mbar_arrive(&sm.full[s]);
+        const int cur_tile = __shfl_sync(0xFFFFFFFFu, cur.tile, 0);
+        if (it >= (uint32_t)STAGES) named_bar_sync(kBarStage + s, kBarThreads);  // every walker has left stage s
+        if (cur_tile < 0) {
+          if (lane == 0) {
+            sm.tile[s] = -1;
+            mbar_arrive(&sm.full[s]);
+          }
           break;
         }
+        if (lane != 0) continue;
         const uint32_t first = (uint32_t)cur.tile * TN;
         const uint32_t rp_bytes = ((cur.cnt + 1) * 4u + 15u) & ~15u;
         sm.tile[s] = cur.tile;
@@ -743,7 +757,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
     long long a_gpu = 0, a_ready = 0, a_def = 0, a_bad = 0, a_key[4] = {0, 0, 0, 0};  // lane 0 only
     for (uint32_t it = warp - kWalkWarps - 1;; it += 2) {
       const int b = it % kRing;
-      mbar_wait_parked(&sm.cnt_full[b], (it / kRing) & 1u);
+      named_bar_sync(kBarCnt + b, kBarThreads);  // the walkers' partial counts of this tile are in part[b]
       const int tile = sm.scan_tile[b];
       if (tile < 0) break;
       GNC_T(5, it, gtimer());
@@ -854,7 +868,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&sm.empty[s]);  // this warp no longer reads the stage
+      named_bar_arrive(kBarStage + s, kBarThreads);  // this warp no longer reads the stage
       if (tid == 0) GNC_T(1, it, gtimer());
 
       // -------- flags, ranks, partial counts; the records go out kRing-1 iterations later --------
@@ -898,8 +912,9 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
           sm.tile_cnt[b] = 0;
           st_volatile_u32(p.agg + tile, ((p.epoch & kEpochMask) << 10) | ((old & 0xFFFFu) + (uint32_t)__popc(gb)));
         }
-        mbar_arrive(&sm.cnt_full[b]);  // the scan warp can start on this tile
       }
+      __syncwarp();
+      named_bar_arrive(kBarCnt + b, kBarThreads);  // the scan warp can start on this tile
       if (is_gpu && wide) {
 #pragma unroll
         for (int k = 0; k < 4; k++) acc128_add(&sm.acc[GNC_C_KEY_LO + k], &sm.acc[GNC_C_KEY_HI + k], wv[k]);
@@ -926,11 +941,10 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
     for (int q = kRing - 2; q >= 0; q--)
       if (it >= (uint32_t)q + 1) emit_stashed(it - (q + 1), lag_first[q]);
     __syncwarp();
-    if (lane == 0) {
-      if (warp == 0) sm.scan_tile[it % kRing] = sm.scan_tile[(it + 1) % kRing] = -1;
-      mbar_arrive(&sm.cnt_full[it % kRing]);
-      mbar_arrive(&sm.cnt_full[(it + 1) % kRing]);
-    }
+    if (tid == 0) sm.scan_tile[it % kRing] = sm.scan_tile[(it + 1) % kRing] = -1;
+    __syncwarp();
+    named_bar_arrive(kBarCnt + (int)(it % kRing), kBarThreads);
+    named_bar_arrive(kBarCnt + (int)((it + 1) % kRing), kBarThreads);
   }
 
   // ------------------------------ grid-wide finish ------------------------------
