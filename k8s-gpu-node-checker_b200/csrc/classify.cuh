@@ -618,7 +618,8 @@ struct Smem {
 template <int TN>
 __host__ __device__ constexpr int cta_threads() { return TN + 96; }
 
-template <int TN, int STAGES, int STAGE_BYTES, int MIN_CTAS>
+// FLEET: the fused multi-GPU gather (peer stores while emitting); compiled out of the single-GPU kernels.
+template <int TN, int STAGES, int STAGE_BYTES, int MIN_CTAS, bool FLEET>
 __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(const __grid_constant__ Params p) {
   using S = Smem<TN, STAGES, STAGE_BYTES>;
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -645,7 +646,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   }
   if (tid < GNC_N_COUNTS) sm.acc[tid] = 0;
   if (tid < kRing) sm.tile_cnt[tid] = 0;
-  if (p.fleet_world && tid < (int)p.fleet_world && p.fleet_ack_need) {
+  if (FLEET && tid < (int)p.fleet_world && p.fleet_ack_need) {
     // the slots about to be rewritten were last filled two launches ago: every peer must have read them
     const unsigned long long t0 = global_ns();
     while (ld_sys_u64(p.fleet_ack + tid) < p.fleet_ack_need)
@@ -659,10 +660,11 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   if (warp == kWalkWarps) {
     // ------------------------------ producer ------------------------------
     {
-      // Tickets are taken kAhead tiles before the tile is copied to shared memory, and the tile's
+      // Tickets are taken kAhead tiles before the tile is copied to shared memory (one is best: more lead
+      // puts ticket order further from completion order and the look-backs wait longer), and the tile's
       // bytes are prefetched into L2 at once: HBM latency is then paid while the stage is still
       // busy with an earlier tile, and the later bulk copy is an L2 hit.
-      constexpr int kAhead = 2, kQ = kAhead + 1;
+      constexpr int kAhead = 1, kQ = kAhead + 1;
       struct Plan {
         int tile;  // -1: no more tiles
         uint32_t lo_al, hi, bytes, cnt;
@@ -806,7 +808,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
             v0 = (short)(sv.x & 0xFFFFu), v1 = (short)(sv.x >> 16), v2 = (short)(sv.y & 0xFFFFu), v3 = (short)(sv.y >> 16);
           }
           p.gpu_idx[pos] = p.node_base + first_e + j;
-          if (p.fleet_world && pos < p.fleet_cap) {
+          if (FLEET && pos < p.fleet_cap) {
             const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + pos;
             for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][at] = p.node_base + first_e + j;
           }
@@ -950,7 +952,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         atomicAdd(&sc->accum[c], sm.acc[c]);
       }
     }
-    if (p.fleet_world) __threadfence_system();  // this CTA's peer stores are out before it counts as done
+    if (FLEET) __threadfence_system();  // this CTA's peer stores are out before it counts as done
     else __threadfence();
     const uint32_t prev = atomicAdd(&sc->done, 1u);
     if (prev == gridDim.x - 1) {  // last CTA: publish the counts block and re-arm the scratch
@@ -960,11 +962,11 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         if (c == GNC_C_SCANNED) v = p.n_nodes;
         p.counts[c] = v;
         sc->accum[c] = 0;
-        if (p.fleet_world)
+        if (FLEET)
           for (uint32_t q = 0; q < p.fleet_world; q++)
             reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[c] = v;
       }
-      if (p.fleet_world) {  // every index and the counts are on their way: raise this rank's flag everywhere
+      if (FLEET) {  // every index and the counts are on their way: raise this rank's flag everywhere
         __threadfence_system();
         for (uint32_t q = 0; q < p.fleet_world; q++) st_sys_u64(p.fleet_flag[q] + p.fleet_rank, p.fleet_epoch);
       }

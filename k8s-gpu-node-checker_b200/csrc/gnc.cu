@@ -27,16 +27,19 @@ struct Variant {
   size_t smem;
   const void* fn;
   void (*launch)(const Params&, int grid, size_t smem, cudaStream_t);
+  const void* fn_fleet;  // same kernel with the fused multi-GPU gather compiled in
+  void (*launch_fleet)(const Params&, int grid, size_t smem, cudaStream_t);
 };
 
-template <int TN, int ST, int SB, int MC>
+template <int TN, int ST, int SB, int MC, bool FLEET>
 void launch_variant(const Params& p, int grid, size_t smem, cudaStream_t stream) {
-  gnc::classify_kernel<TN, ST, SB, MC><<<grid, gnc::cta_threads<TN>(), smem, stream>>>(p);
+  gnc::classify_kernel<TN, ST, SB, MC, FLEET><<<grid, gnc::cta_threads<TN>(), smem, stream>>>(p);
 }
 template <int TN, int ST, int SB, int MC>
 Variant make_variant(const char* name) {
   return Variant{name, TN, SB, gnc::cta_threads<TN>(), sizeof(gnc::Smem<TN, ST, SB>),
-                 (const void*)gnc::classify_kernel<TN, ST, SB, MC>, launch_variant<TN, ST, SB, MC>};
+                 (const void*)gnc::classify_kernel<TN, ST, SB, MC, false>, launch_variant<TN, ST, SB, MC, false>,
+                 (const void*)gnc::classify_kernel<TN, ST, SB, MC, true>, launch_variant<TN, ST, SB, MC, true>};
 }
 
 // Ordered by preference: the first whose stage holds an average tile with 5 % to spare is used.
@@ -283,6 +286,7 @@ int gnc_create(gnc_ctx** out, int device, int rank, int world, const void* nccl_
   c->sm_count = prop.multiProcessorCount;
   for (int v = 0; v < kNumVariants; v++) {
     CUDA_TRY(c, cudaFuncSetAttribute(kVariants[v].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVariants[v].smem));
+    CUDA_TRY(c, cudaFuncSetAttribute(kVariants[v].fn_fleet, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVariants[v].smem));
     int n = 0;
     CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kVariants[v].fn, kVariants[v].threads, kVariants[v].smem));
     if (n < 1) return fail(c, GNC_ERR_STATE, std::string("kernel variant does not fit an SM: ") + kVariants[v].name);
@@ -368,7 +372,8 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
 #endif
   if (c->fleet.on) fleet_params(c, &p);
   const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(c->sm_count * c->ctas_per_sm[v]));
-  var.launch(p, grid, var.smem, stream);
+  if (c->fleet.on) var.launch_fleet(p, grid, var.smem, stream);
+  else var.launch(p, grid, var.smem, stream);
   CUDA_TRY(c, cudaGetLastError());
   c->launches++;
   return GNC_OK;
