@@ -1028,7 +1028,7 @@ int device_exclusive_scan(gnc_ctx* c, const T* in, unsigned long long n, T* out,
   }
   const unsigned long long nb = (n + 1023) / 1024;
   gnc::js::scan_block_totals<T, Op><<<(unsigned)nb, 1024, 0, stream>>>(in, n, block_totals, op, ident);
-  gnc::js::scan_totals_serial<T, Op><<<1, 1, 0, stream>>>(block_totals, nb, op, ident, grand);
+  gnc::js::scan_totals_block<T, Op><<<1, 1024, 0, stream>>>(block_totals, nb, op, ident, grand);
   gnc::js::scan_apply<T, Op><<<(unsigned)nb, 1024, 0, stream>>>(in, n, block_totals, out, op, ident);
   CUDA_TRY(c, cudaGetLastError());
   c->launches += 3;
@@ -1052,10 +1052,12 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
   const size_t nbc = (n_chunks + 1023) / 1024 + 1, nbn = (nodes_cap + 1023) / 1024 + 1;
+  const size_t mask_bytes = (size_t)n_chunks * kChunk;  // the structural index: one byte per document byte
   const size_t o_work = take(sizeof(Work)), o_funcs = take(n_chunks), o_pf = take(n_chunks), o_bt8 = take(nbc),
                o_delta = take(n_chunks * 4), o_depth = take(n_chunks * 4), o_bt32 = take(nbc * 4), o_evc = take(n_chunks * 4),
                o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
-               o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8);
+               o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8),
+               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
   if (off > c->json_scratch_bytes) {
     if (c->json_scratch) {
       CUDA_TRY(c, cudaStreamSynchronize(stream));
@@ -1076,30 +1078,36 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
                      *total = (unsigned long long*)(base + o_total);
   unsigned int* sizes = (unsigned int*)(base + o_sizes);
   NodePlan* plans = (NodePlan*)(base + o_plans);
+  Masks mk;
+  mk.w = (uint4*)(base + o_masks);
+  int* min_rel = (int*)(base + o_minrel);
+  uint2* desc = (uint2*)(base + o_desc);
   if (!aligned16(json)) return fail(c, GNC_ERR_ARG, "json must be 16-byte aligned");
   CUDA_TRY(c, cudaMemsetAsync(work, 0, sizeof(Work), stream));
   int rc;
   const unsigned cb = (unsigned)((n_chunks + 255) / 256);
   if (n_chunks) {
-    lex_funcs_kernel<<<cb, 256, 0, stream>>>(json, n, funcs, n_chunks);
+    const unsigned tb = (unsigned)((n_chunks + kTileChunks - 1) / kTileChunks);
+    constexpr size_t kTileSmem = (size_t)kTileChunks * kRowStride;
+    lex_summary_kernel<<<tb, kTileChunks, kTileSmem, stream>>>(json, n, funcs, n_chunks);
     if ((rc = device_exclusive_scan<uint8_t, OpCompose>(c, funcs, n_chunks, pf, bt8, nullptr, OpCompose(), (uint8_t)kIdentity, stream))) return rc;
-    depth_delta_kernel<<<cb, 256, 0, stream>>>(json, n, pf, delta, n_chunks);
+    index_kernel<<<tb, kTileChunks, kTileSmem, stream>>>(json, n, pf, mk, delta, min_rel, n_chunks);
     if ((rc = device_exclusive_scan<int, OpAddI>(c, delta, n_chunks, depth0, bt32, nullptr, OpAddI(), 0, stream))) return rc;
-    events_kernel<<<cb, 256, 0, stream>>>(json, n, pf, depth0, evc, work, n_chunks);
+    events_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, min_rel, evc, work, n_chunks);
     if ((rc = device_exclusive_scan<unsigned int, OpAddU>(c, evc, n_chunks, evp, btu, nullptr, OpAddU(), 0u, stream))) return rc;
-    pick_items_kernel<<<1, 1, 0, stream>>>(json, n, pf, depth0, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
-    element_starts_kernel<<<cb, 256, 0, stream>>>(json, n, pf, depth0, evp, work, elem, n_chunks);
+    pick_items_kernel<<<1, 1, 0, stream>>>(json, n, mk, depth0, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
+    element_starts_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, evp, work, elem, n_chunks);
     c->launches += 5;
   }
   const unsigned nb = (unsigned)std::max<unsigned long long>(1, (nodes_cap + 127) / 128);
   if (nodes_cap) {
     CUDA_TRY(c, cudaMemsetAsync(sizes, 0, (nodes_cap + 1) * 4, stream));
-    measure_rows_kernel<<<nb, 128, 0, stream>>>(json, n, elem, work, sizes, plans);
+    measure_rows_kernel<<<nb, 128, 0, stream>>>(json, n, mk, elem, work, sizes, plans, desc);
     strip_flag_kernel<<<(unsigned)((nodes_cap + 255) / 256), 256, 0, stream>>>(sizes, plain, (unsigned int)nodes_cap);
     c->launches += 2;
   }
   if ((rc = device_exclusive_scan<unsigned long long, OpAddULL>(c, plain, nodes_cap, offs, bt64, total, OpAddULL(), 0ull, stream))) return rc;
-  write_rows_kernel<<<nb, 128, 0, stream>>>(json, n, plans, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
+  write_rows_kernel<<<nb, kWriteThreads, kWriteStage, stream>>>(json, n, mk, plans, desc, elem, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
   CUDA_TRY(c, cudaGetLastError());
   c->launches += 1;
   return GNC_OK;

@@ -6,16 +6,25 @@
 // `type` / `status` of each element of `status.conditions` (:173-177) -- with json.loads semantics
 // (duplicate object keys: last wins; \uXXXX escapes, surrogate pairs joined, lone surrogates kept).
 //
-// Structure (all data-parallel until the per-node parse):
-//   1. lexer:   256-byte chunks; each chunk's effect on the 3-state string lexer is a function
-//               {outside, in string, after backslash} -> state; an exclusive scan of function
-//               compositions gives every chunk its start state
-//   2. depth:   per-chunk bracket balance outside strings, exclusive sum scan -> start depth
+// Structure: a structural index first (bit masks, one bit per byte), then everything walks the masks.
+//   1. summary: 256-byte chunks staged through shared memory; per 32-byte group the quote and backslash
+//               bit masks (SWAR byte compares); each chunk's effect on the lexer state {escape pending,
+//               inside string} as a function table; an exclusive scan of function COMPOSITIONS gives
+//               every chunk its start state
+//   2. index:   with the start state known: escaped bytes, unescaped quotes, in-string mask (prefix
+//               xor), and from them six masks per group -- string opens, string closes, brackets open /
+//               close outside strings, commas outside strings, backslashes inside strings -- plus the
+//               chunk's bracket balance; a sum scan gives every chunk its start depth
 //   3. events:  element separators of root-level arrays (the '[' itself and each ',' at depth 2) are
-//               counted per chunk and scanned; root-level array brackets are listed; one thread then
-//               picks the LAST root key "items" and the range of events that are its elements
-//   4. nodes:   one thread per element parses its node (a small recursive-descent walker over the
-//               bytes), first to measure its PNL row, then -- after a scan of row sizes -- to write it
+//               counted per chunk from the masks and scanned; root-level array brackets are listed; one
+//               thread then picks the LAST root key "items" and the range of events that are its elements
+//   4. nodes:   one thread per element.  The fast walker steps from structural bit to structural bit
+//               (find-first-set over the masks; containers that do not matter are skipped a group at a
+//               time by popcount) and touches document bytes only to compare the few keys that matter
+//               and to copy capacity / condition text.  Anything unusual in the parts that matter -- an
+//               escape in a key or value, a duplicate of a key that matters, a non-string quantity -- sends
+//               that node to the general byte-serial parser below, which implements the full semantics.
+//               Two passes (measure, scan of row sizes, write).
 #pragma once
 
 #include <cuda_runtime.h>
@@ -24,10 +33,14 @@
 namespace gnc {
 namespace js {
 
-constexpr int kChunk = 256;
+constexpr int kChunk = 256;            // bytes per thread in the chunk passes
+constexpr int kGroup = 32;             // bytes per mask word
+constexpr int kGroupsPerChunk = kChunk / kGroup;
+constexpr int kTileChunks = 128;       // chunks per CTA in the byte passes (one per thread)
+constexpr int kRowStride = kChunk + 16;  // shared-memory row pitch: 16-byte reads by 8 adjacent threads hit 8 different bank quads
 constexpr int kMaxRootArrays = 64;
 
-enum : int { INFO_NODES = 0, INFO_ROWS_BYTES = 1, INFO_STATUS = 2, INFO_ITEMS_BEGIN = 3, INFO_ITEMS_END = 4, INFO_N = 8 };
+enum : int { INFO_NODES = 0, INFO_ROWS_BYTES = 1, INFO_STATUS = 2, INFO_ITEMS_BEGIN = 3, INFO_ITEMS_END = 4, INFO_GENERAL_NODES = 5, INFO_N = 8 };
 enum : int { ST_NO_ITEMS = 1, ST_NODES_CAP = 2, ST_ROWS_CAP = 4, ST_BAD_JSON = 8, ST_TOO_MANY_ROOT_ARRAYS = 16 };
 
 struct Work {                 // device scratch, one per call
@@ -38,92 +51,208 @@ struct Work {                 // device scratch, one per call
   unsigned long long ev_base;                     // rank of the event at items_begin
   unsigned int n_nodes;
   unsigned int status;
+  unsigned int general_nodes;                     // nodes that went through the byte-serial parser
 };
 
-// ---- lexer -------------------------------------------------------------------------------------
-__device__ __forceinline__ int lex_step(int st, uint32_t c) {
-  if (st == 0) return c == '"' ? 1 : 0;
-  if (st == 1) return c == '\\' ? 2 : (c == '"' ? 0 : 1);
-  return 1;
-}
-// a chunk's transition function, 2 bits per start state
-__device__ __forceinline__ uint32_t compose(uint32_t f, uint32_t g) {  // first f, then g
-  return ((g >> (2 * (f & 3))) & 3) | (((g >> (2 * ((f >> 2) & 3))) & 3) << 2) | (((g >> (2 * ((f >> 4) & 3))) & 3) << 4);
-}
-constexpr uint32_t kIdentity = 0 | (1 << 2) | (2 << 4);
+// The structural index: 32 bytes per 32 document bytes (group g -> w[2g], w[2g + 1]); bit i of a mask = byte 32 g + i.
+//   w[2g]     = { opening quotes, closing quotes, '{' '[' outside strings, '}' ']' outside strings }
+//   w[2g + 1] = { ',' outside strings, backslashes inside strings, 0, 0 }
+// One 32-byte sector per group: the node walkers, one thread per node at scattered places, fetch every sector once.
+struct Masks {
+  uint4* w;
+};
 
-// Bytes of chunk c in order, fetched 16 at a time (the document is 16-byte aligned; the last,
-// partial chunk is read bytewise).
-template <class F>
-__device__ __forceinline__ void for_chunk_bytes(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long c, F&& f) {
-  const unsigned long long b = c * kChunk, e = min(n, b + kChunk);
-  if (e - b == kChunk) {
-    const uint4* v = reinterpret_cast<const uint4*>(json + b);
-#pragma unroll 4
-    for (int q = 0; q < kChunk / 16; q++) {
-      const uint4 x = __ldg(v + q);
-      const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+// ---- lexer state ---------------------------------------------------------------------------------
+// State = e | s << 1: e = the first byte of the chunk is escaped by a backslash before it, s = the chunk
+// starts inside a string.  A chunk's transition function holds 2 bits per start state.  (Backslashes
+// are taken as escapes wherever they stand; in valid JSON they only occur inside strings.)
+__device__ __forceinline__ uint32_t compose(uint32_t f, uint32_t g) {  // first f, then g
+  return ((g >> (2 * (f & 3))) & 3) | (((g >> (2 * ((f >> 2) & 3))) & 3) << 2) | (((g >> (2 * ((f >> 4) & 3))) & 3) << 4) |
+         (((g >> (2 * ((f >> 6) & 3))) & 3) << 6);
+}
+constexpr uint32_t kIdentity = 0 | (1 << 2) | (2 << 4) | (3 << 6);
+
+// ---- SWAR byte compares ----------------------------------------------------------------------------
+// 0x80 in every byte of w that equals the byte replicated in k4 (exact: no borrow between bytes)
+__device__ __forceinline__ uint32_t eq_bytes(uint32_t w, uint32_t k4) {
+  const uint32_t x = w ^ k4;
+  const uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
+  return ~(t | x) & 0x80808080u;
+}
+// the four 0x80 flags of z as a nibble, byte 0 in bit 0 (the partial products never collide)
+__device__ __forceinline__ uint32_t flags_to_nibble(uint32_t z) { return (z * 0x00204081u) >> 28; }
+
+struct RawMasks {
+  uint32_t q, b, o, c, k;
+};
+template <bool ALL>
+__device__ __forceinline__ RawMasks raw_masks(const uint4 lo, const uint4 hi) {
+  const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+  RawMasks m = {0, 0, 0, 0, 0};
 #pragma unroll
-      for (int k = 0; k < 16; k++) f(b + 16 * q + k, (w[k >> 2] >> (8 * (k & 3))) & 0xFFu);
+  for (int i = 0; i < 8; i++) {
+    m.q |= flags_to_nibble(eq_bytes(w[i], 0x22222222u)) << (4 * i);
+    m.b |= flags_to_nibble(eq_bytes(w[i], 0x5C5C5C5Cu)) << (4 * i);
+    if (ALL) {
+      const uint32_t folded = w[i] & 0xDFDFDFDFu;  // '{' -> '[', '}' -> ']' (nothing else lands on them)
+      m.o |= flags_to_nibble(eq_bytes(folded, 0x5B5B5B5Bu)) << (4 * i);
+      m.c |= flags_to_nibble(eq_bytes(folded, 0x5D5D5D5Du)) << (4 * i);
+      m.k |= flags_to_nibble(eq_bytes(w[i], 0x2C2C2C2Cu)) << (4 * i);
     }
-  } else {
-    for (unsigned long long i = b; i < e; i++) f(i, (uint32_t)json[i]);
+  }
+  return m;
+}
+
+// Bytes escaped by a backslash, given the backslash mask of a group and whether its first byte is
+// escaped from the group before.  An unescaped backslash escapes the byte after it, whatever that is;
+// pe becomes whether the next group's first byte is escaped.  One iteration per escape sequence.
+__device__ __forceinline__ uint32_t escaped_bytes(uint32_t backslash, uint32_t& pe) {
+  if ((backslash | pe) == 0) return 0;
+  uint32_t esc = pe, rem = backslash & ~pe;
+  pe = 0;
+  while (rem) {
+    const int p = __ffs(rem) - 1;
+    if (p == 31) {
+      pe = 1;
+      break;
+    }
+    esc |= 2u << p;
+    rem &= ~(3u << p);
+  }
+  return esc;
+}
+__device__ __forceinline__ uint32_t prefix_xor(uint32_t x) {
+  x ^= x << 1;
+  x ^= x << 2;
+  x ^= x << 4;
+  x ^= x << 8;
+  x ^= x << 16;
+  return x;
+}
+
+// Stage one tile of the document (kTileChunks chunks of 256 B) into shared memory, coalesced; bytes past
+// the end of the document read as spaces.
+__device__ __forceinline__ void stage_tile(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long tile_chunk0,
+                                           uint8_t* sh) {
+  const unsigned long long base = tile_chunk0 * kChunk;
+  constexpr int kVecs = kTileChunks * kChunk / 16;
+  for (int i = threadIdx.x; i < kVecs; i += blockDim.x) {
+    const unsigned long long at = base + 16ull * i;
+    uint4 v = make_uint4(0x20202020u, 0x20202020u, 0x20202020u, 0x20202020u);
+    if (at + 16 <= n) {
+      v = __ldg(reinterpret_cast<const uint4*>(json + at));
+    } else if (at < n) {
+      uint8_t tmp[16];
+      for (int k = 0; k < 16; k++) tmp[k] = at + k < n ? json[at + k] : (uint8_t)0x20;
+      memcpy(&v, tmp, 16);
+    }
+    *reinterpret_cast<uint4*>(sh + (i >> 4) * kRowStride + (i & 15) * 16) = v;
   }
 }
 
-__global__ void lex_funcs_kernel(const uint8_t* __restrict__ json, unsigned long long n, uint8_t* __restrict__ funcs,
-                                 unsigned long long n_chunks) {
-  const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+// pass 1: each chunk's transition function
+__global__ void __launch_bounds__(kTileChunks) lex_summary_kernel(const uint8_t* __restrict__ json, unsigned long long n,
+                                                                  uint8_t* __restrict__ funcs, unsigned long long n_chunks) {
+  extern __shared__ __align__(16) uint8_t sh[];
+  const unsigned long long chunk0 = (unsigned long long)blockIdx.x * kTileChunks;
+  stage_tile(json, n, chunk0, sh);
+  __syncthreads();
+  const unsigned long long c = chunk0 + threadIdx.x;
   if (c >= n_chunks) return;
-  int s0 = 0, s1 = 1, s2 = 2;
-  for_chunk_bytes(json, n, c, [&](unsigned long long, uint32_t ch) {
-    s0 = lex_step(s0, ch);
-    s1 = lex_step(s1, ch);
-    s2 = lex_step(s2, ch);
-  });
-  funcs[c] = (uint8_t)(s0 | (s1 << 2) | (s2 << 4));
+  const uint4* row = reinterpret_cast<const uint4*>(sh + threadIdx.x * kRowStride);
+  uint32_t pe0 = 0, pe1 = 1, par0 = 0, par1 = 0;  // escape carry and quote parity, for e = 0 and e = 1 at the chunk start
+#pragma unroll 2
+  for (int g = 0; g < kGroupsPerChunk; g++) {
+    const RawMasks m = raw_masks<false>(row[2 * g], row[2 * g + 1]);
+    const bool same = pe0 == pe1;
+    const uint32_t q0 = m.q & ~escaped_bytes(m.b, pe0);
+    par0 ^= __popc(q0) & 1;
+    if (same) {
+      pe1 = pe0;
+      par1 ^= __popc(q0) & 1;
+    } else {
+      const uint32_t q1 = m.q & ~escaped_bytes(m.b, pe1);
+      par1 ^= __popc(q1) & 1;
+    }
+  }
+  // f(e | s << 1) = pe_e | (s ^ par_e) << 1
+  const uint32_t f0 = pe0 | (par0 << 1), f1 = pe1 | (par1 << 1), f2 = pe0 | ((par0 ^ 1u) << 1), f3 = pe1 | ((par1 ^ 1u) << 1);
+  funcs[c] = (uint8_t)(f0 | (f1 << 2) | (f2 << 4) | (f3 << 6));
 }
 
-// ---- generic 3-kernel exclusive scan over n items, 1024 per block ---------------------------------
+// pass 2: the six masks of every group, the chunk's bracket balance, and a lower bound of the balance inside it
+__global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __restrict__ json, unsigned long long n,
+                                                            const uint8_t* __restrict__ pf, Masks mk, int* __restrict__ delta,
+                                                            int* __restrict__ min_rel, unsigned long long n_chunks) {
+  extern __shared__ __align__(16) uint8_t sh[];
+  const unsigned long long chunk0 = (unsigned long long)blockIdx.x * kTileChunks;
+  stage_tile(json, n, chunk0, sh);
+  __syncthreads();
+  const unsigned long long c = chunk0 + threadIdx.x;
+  if (c >= n_chunks) return;
+  const uint4* row = reinterpret_cast<const uint4*>(sh + threadIdx.x * kRowStride);
+  const uint32_t st = pf[c] & 3u;  // (composition of all earlier chunks)(state 0)
+  uint32_t pe = st & 1u, in_str = (st >> 1) ? 0xFFFFFFFFu : 0u;
+  uint4* out = mk.w + c * (2 * kGroupsPerChunk);
+  int bal = 0, low = 0;
+#pragma unroll
+  for (int g = 0; g < kGroupsPerChunk; g++) {
+    const RawMasks m = raw_masks<true>(row[2 * g], row[2 * g + 1]);
+    const uint32_t q = m.q & ~escaped_bytes(m.b, pe);
+    const uint32_t s = prefix_xor(q) ^ in_str;  // bit i: byte i is inside a string (opening quote included, closing quote not)
+    in_str = (s >> 31) ? 0xFFFFFFFFu : 0u;
+    const uint32_t o = m.o & ~s, cl = m.c & ~s;
+    out[2 * g] = make_uint4(q & s, q & ~s, o, cl);
+    out[2 * g + 1] = make_uint4(m.k & ~s, m.b & s, 0u, 0u);
+    low = min(low, bal - __popc(cl));  // as if every close of the group came first
+    bal += __popc(o) - __popc(cl);
+  }
+  delta[c] = bal;
+  min_rel[c] = low;
+}
+
+// ---- generic exclusive scan over n items, 1024 per block: block totals, scan of totals, apply ---------
+template <class T, class Op>
+__device__ __forceinline__ T block_inclusive_scan_1024(T v, T* sh, Op op) {
+  sh[threadIdx.x] = v;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const T t = threadIdx.x >= d ? op(sh[threadIdx.x - d], sh[threadIdx.x]) : sh[threadIdx.x];
+    __syncthreads();
+    sh[threadIdx.x] = t;
+    __syncthreads();
+  }
+  return sh[threadIdx.x];
+}
 template <class T, class Op>
 __global__ void scan_block_totals(const T* __restrict__ in, unsigned long long n, T* __restrict__ totals, Op op, T ident) {
   __shared__ T sh[1024];
   const unsigned long long i = blockIdx.x * 1024ull + threadIdx.x;
-  sh[threadIdx.x] = i < n ? in[i] : ident;
-  __syncthreads();
-  for (int d = 1; d < 1024; d <<= 1) {
-    T v = threadIdx.x >= d ? op(sh[threadIdx.x - d], sh[threadIdx.x]) : sh[threadIdx.x];
-    __syncthreads();
-    sh[threadIdx.x] = v;
-    __syncthreads();
-  }
-  if (threadIdx.x == 1023) totals[blockIdx.x] = sh[1023];
+  const T incl = block_inclusive_scan_1024<T, Op>(i < n ? in[i] : ident, sh, op);
+  if (threadIdx.x == 1023) totals[blockIdx.x] = incl;
 }
+// one block: thread t owns a contiguous run of the totals (order matters: composition does not commute)
 template <class T, class Op>
-__global__ void scan_totals_serial(T* totals, unsigned long long nb, Op op, T ident, T* grand) {
-  // one thread: nb is n/1024, a few thousand at most
+__global__ void scan_totals_block(T* totals, unsigned long long nb, Op op, T ident, T* grand) {
+  __shared__ T sh[1024];
+  const unsigned long long per = (nb + 1023) / 1024, lo = min(nb, threadIdx.x * per), hi = min(nb, lo + per);
   T run = ident;
-  for (unsigned long long b = 0; b < nb; b++) {
-    T t = totals[b];
-    totals[b] = run;
-    run = op(run, t);
+  for (unsigned long long b = lo; b < hi; b++) run = op(run, totals[b]);
+  const T incl = block_inclusive_scan_1024<T, Op>(run, sh, op);
+  T before = threadIdx.x ? sh[threadIdx.x - 1] : ident;
+  if (grand && threadIdx.x == 1023) *grand = incl;
+  for (unsigned long long b = lo; b < hi; b++) {
+    const T t = totals[b];
+    totals[b] = before;
+    before = op(before, t);
   }
-  if (grand) *grand = run;
 }
 template <class T, class Op>
 __global__ void scan_apply(const T* __restrict__ in, unsigned long long n, const T* __restrict__ totals, T* __restrict__ out,
                            Op op, T ident) {
   __shared__ T sh[1024];
   const unsigned long long i = blockIdx.x * 1024ull + threadIdx.x;
-  const T mine = i < n ? in[i] : ident;
-  sh[threadIdx.x] = mine;
-  __syncthreads();
-  for (int d = 1; d < 1024; d <<= 1) {
-    T v = threadIdx.x >= d ? op(sh[threadIdx.x - d], sh[threadIdx.x]) : sh[threadIdx.x];
-    __syncthreads();
-    sh[threadIdx.x] = v;
-    __syncthreads();
-  }
+  block_inclusive_scan_1024<T, Op>(i < n ? in[i] : ident, sh, op);
   // exclusive: everything before me in the block, after the block's own prefix
   const T before = threadIdx.x ? sh[threadIdx.x - 1] : ident;
   if (i < n) out[i] = op(totals[blockIdx.x], before);
@@ -141,54 +270,77 @@ struct OpAddULL {
   __device__ unsigned long long operator()(unsigned long long a, unsigned long long b) const { return a + b; }
 };
 
-// start state of a chunk = (composition of all earlier chunks)(state 0)
-__device__ __forceinline__ int start_state(const uint8_t* prefix_funcs, unsigned long long c) { return prefix_funcs[c] & 3; }
-
-// Visit the bytes of chunk c that lie outside strings: f(pos, byte, depth_before); brackets move depth.
+// ---- events ------------------------------------------------------------------------------------------
+// Visit, in order, the brackets and commas outside strings of chunk c that lie before `limit`:
+// f(pos, kind, depth_before) with kind 0 open, 1 close, 2 comma.  Groups that stay deeper than the root
+// levels are passed over by popcount.  Returns the depth after the last byte visited.
 template <class F>
-__device__ __forceinline__ int visit_chunk(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long c, int st,
-                                           int depth, F&& f) {
-  for_chunk_bytes(json, n, c, [&](unsigned long long i, uint32_t ch) {
-    if (st == 0) {
-      if (ch == '"') {
-        st = 1;
-      } else {
-        f(i, ch, depth);
-        if (ch == '{' || ch == '[') depth++;
-        else if (ch == '}' || ch == ']') depth--;
-      }
-    } else {
-      st = lex_step(st, ch);
+__device__ __forceinline__ int visit_structurals(const Masks& mk, unsigned long long c, int depth, unsigned long long limit, F&& f) {
+  const uint4* pw = mk.w + c * (2 * kGroupsPerChunk);
+  uint32_t ow[8], cw[8], kw[8];
+#pragma unroll
+  for (int g = 0; g < kGroupsPerChunk; g++) {
+    const uint4 a = __ldg(pw + 2 * g);
+    ow[g] = a.z, cw[g] = a.w;
+    kw[g] = __ldg(reinterpret_cast<const uint32_t*>(pw + 2 * g + 1));
+  }
+#pragma unroll
+  for (int g = 0; g < kGroupsPerChunk; g++) {
+    const unsigned long long base = (c * kGroupsPerChunk + g) * (unsigned long long)kGroup;
+    if (base >= limit) break;
+    uint32_t o = ow[g], cl = cw[g], k = kw[g];
+    if (limit - base < 32) {
+      const uint32_t keep = (1u << (unsigned)(limit - base)) - 1u;
+      o &= keep, cl &= keep, k &= keep;
     }
-  });
+    if (depth - __popc(cl) > 2) {
+      depth += __popc(o) - __popc(cl);
+      continue;
+    }
+    uint32_t any = o | cl | k;
+    while (any) {
+      const int bit = __ffs(any) - 1;
+      const uint32_t bm = 1u << bit;
+      any &= any - 1;
+      if (o & bm) {
+        f(base + bit, 0, depth);
+        depth++;
+      } else if (cl & bm) {
+        f(base + bit, 1, depth);
+        depth--;
+      } else {
+        f(base + bit, 2, depth);
+      }
+    }
+  }
   return depth;
 }
 
-__global__ void depth_delta_kernel(const uint8_t* __restrict__ json, unsigned long long n, const uint8_t* __restrict__ pf,
-                                   int* __restrict__ delta, unsigned long long n_chunks) {
-  const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-  if (c >= n_chunks) return;
-  delta[c] = visit_chunk(json, n, c, start_state(pf, c), 0, [](unsigned long long, uint32_t, int) {});
-}
-
 // events: the '[' of every root-level array and every ',' directly inside one (depth 2 outside strings)
-__global__ void events_kernel(const uint8_t* __restrict__ json, unsigned long long n, const uint8_t* __restrict__ pf,
-                              const int* __restrict__ depth0, unsigned int* __restrict__ ev_count, Work* w,
-                              unsigned long long n_chunks) {
+__global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
+                              const int* __restrict__ min_rel, unsigned int* __restrict__ ev_count, Work* w, unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
   if (c >= n_chunks) return;
   unsigned int cnt = 0;
-  visit_chunk(json, n, c, start_state(pf, c), depth0[c], [&](unsigned long long pos, uint32_t ch, int d) {
-    if (ch == '[' && d == 1) {
+  if (depth0[c] + min_rel[c] > 2) {  // the whole chunk lies deeper than the root levels
+    ev_count[c] = 0;
+    return;
+  }
+  visit_structurals(mk, c, depth0[c], ~0ull, [&](unsigned long long pos, int kind, int d) {
+    if (kind == 0 && d == 1) {
+      if (json[pos] == '[') {
+        cnt++;
+        const unsigned int k = atomicAdd(&w->n_open, 1u);
+        if (k < kMaxRootArrays) w->root_open[k] = pos;
+      }
+    } else if (kind == 2 && d == 2) {
       cnt++;
-      const unsigned int k = atomicAdd(&w->n_open, 1u);
-      if (k < kMaxRootArrays) w->root_open[k] = pos;
-    } else if (ch == ',' && d == 2) {
-      cnt++;
-    } else if (ch == ']' && d == 2) {
-      const unsigned int k = atomicAdd(&w->n_close, 1u);
-      if (k < kMaxRootArrays) w->root_close[k] = pos;
-    } else if ((ch == '}' || ch == ']') && d <= 0) {
+    } else if (kind == 1 && d == 2) {
+      if (json[pos] == ']') {
+        const unsigned int k = atomicAdd(&w->n_close, 1u);
+        if (k < kMaxRootArrays) w->root_close[k] = pos;
+      }
+    } else if (kind == 1 && d <= 0) {
       atomicOr(&w->status, (unsigned int)ST_BAD_JSON);
     }
   });
@@ -196,20 +348,19 @@ __global__ void events_kernel(const uint8_t* __restrict__ json, unsigned long lo
 }
 
 // number of events strictly before byte `pos` (pos lies outside strings)
-__device__ unsigned long long events_before(const uint8_t* json, unsigned long long n, const uint8_t* pf, const int* depth0,
-                                            const unsigned int* ev_prefix, unsigned long long pos) {
+__device__ unsigned long long events_before(const uint8_t* json, const Masks& mk, const int* depth0, const unsigned int* ev_prefix,
+                                            unsigned long long pos) {
   const unsigned long long c = pos / kChunk;
   unsigned long long cnt = ev_prefix[c];
-  visit_chunk(json, min(n, pos), c, start_state(pf, c), depth0[c], [&](unsigned long long, uint32_t ch, int d) {
-    if ((ch == '[' && d == 1) || (ch == ',' && d == 2)) cnt++;
+  visit_structurals(mk, c, depth0[c], pos, [&](unsigned long long at, int kind, int d) {
+    if ((kind == 0 && d == 1 && json[at] == '[') || (kind == 2 && d == 2)) cnt++;
   });
   return cnt;
 }
 
 // One thread: which root-level array is the value of the LAST key "items", and which events are its elements.
-__global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned long long n, const uint8_t* __restrict__ pf,
-                                  const int* __restrict__ depth0, const unsigned int* __restrict__ ev_prefix, Work* w,
-                                  unsigned int nodes_cap) {
+__global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const int* __restrict__ depth0,
+                                  const unsigned int* __restrict__ ev_prefix, Work* w, unsigned int nodes_cap) {
   if (w->n_open > kMaxRootArrays || w->n_close > kMaxRootArrays) {
     w->status |= ST_TOO_MANY_ROOT_ARRAYS;
     w->n_nodes = 0;
@@ -244,8 +395,8 @@ __global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned lon
   }
   w->items_begin = (unsigned long long)best;
   w->items_end = end;
-  w->ev_base = events_before(json, n, pf, depth0, ev_prefix, (unsigned long long)best);
-  unsigned long long cnt = events_before(json, n, pf, depth0, ev_prefix, end) - w->ev_base;   // '[' + commas
+  w->ev_base = events_before(json, mk, depth0, ev_prefix, (unsigned long long)best);
+  unsigned long long cnt = events_before(json, mk, depth0, ev_prefix, end) - w->ev_base;   // '[' + commas
   // an empty array has the '[' event but no element
   unsigned long long j = (unsigned long long)best + 1;
   while (j < end && (json[j] == ' ' || json[j] == '\t' || json[j] == '\n' || json[j] == '\r')) j++;
@@ -258,23 +409,24 @@ __global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned lon
 }
 
 // position of the byte after each element's separator
-__global__ void element_starts_kernel(const uint8_t* __restrict__ json, unsigned long long n, const uint8_t* __restrict__ pf,
-                                      const int* __restrict__ depth0, const unsigned int* __restrict__ ev_prefix, const Work* w,
+__global__ void element_starts_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
+                                      const unsigned int* __restrict__ ev_prefix, const Work* w,
                                       unsigned long long* __restrict__ elem_pos, unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
   if (c >= n_chunks) return;
   const unsigned long long lo = w->ev_base, hi = lo + w->n_nodes;
   unsigned long long rank = ev_prefix[c];
   if (rank >= hi) return;
-  visit_chunk(json, n, c, start_state(pf, c), depth0[c], [&](unsigned long long pos, uint32_t ch, int d) {
-    if ((ch == '[' && d == 1) || (ch == ',' && d == 2)) {
+  if (c + 1 < n_chunks && (ev_prefix[c + 1] <= lo || ev_prefix[c + 1] == rank)) return;  // no event of the items array here
+  visit_structurals(mk, c, depth0[c], ~0ull, [&](unsigned long long pos, int kind, int d) {
+    if ((kind == 0 && d == 1 && json[pos] == '[') || (kind == 2 && d == 2)) {
       if (rank >= lo && rank < hi) elem_pos[rank - lo] = pos + 1;
       rank++;
     }
   });
 }
 
-// ---- per-node parser ---------------------------------------------------------------------------------
+// ---- general per-node parser (byte-serial; full json.loads semantics) ---------------------------------------------------------------------------------
 struct Cur {
   const uint8_t* p;
   unsigned long long i, n;
@@ -624,6 +776,7 @@ __device__ void emit_conditions(Cur c, RowOut& o) {  // cursor at '[' of the con
 struct NodePlan {
   unsigned long long cap_pos, cond_pos;  // '{' of status.capacity and '[' of status.conditions, ~0 if none
   unsigned int n_cap, n_cond;
+  unsigned int fast, pad_;               // fast: the structural-index walker handled this node
 };
 
 // Locate the element's status.capacity object and status.conditions array (last duplicates win).
@@ -647,16 +800,301 @@ __device__ void node_emit(const uint8_t* json, unsigned long long n, const NodeP
   if (pl.cond_pos != ~0ull) emit_conditions(Cur{json, pl.cond_pos, n}, o);
 }
 
+// ---- fast walker over the structural index --------------------------------------------------------------
+// One flat state machine, one step per loop iteration: consume the next structural bit of the current
+// group, or move to the next group, or (while skipping a container) pass a whole group by popcount.
+// Every lane of a warp runs the same loop, so lanes at different places in their nodes stay converged;
+// a recursive-descent walker here ran at 1.4 active lanes per warp.
+enum : int { SK_STR_OPEN = 0, SK_STR_CLOSE = 1, SK_OPEN = 2, SK_CLOSE = 3, SK_COMMA = 4 };
+enum : int { L_NODE = 0, L_STATUS = 1, L_CAP = 2, L_CONDS = 3, L_COND = 4, L_ITEM = 5 };
+enum : int { KEY_OTHER = 0, KEY_A = 1, KEY_B = 2 };  // NODE: A status.  STATUS: A capacity, B conditions.  COND: A type, B status.
+
+__host__ __device__ constexpr uint32_t le4(char a, char b = 0, char c = 0, char d = 0) {
+  return (uint32_t)(uint8_t)a | (uint32_t)(uint8_t)b << 8 | (uint32_t)(uint8_t)c << 16 | (uint32_t)(uint8_t)d << 24;
+}
+
+// the twelve document bytes from `at` on, as three little-endian words (zeros past the end)
+__device__ __forceinline__ void key_words(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long at, uint32_t& k0,
+                                          uint32_t& k1, uint32_t& k2) {
+  const unsigned long long base = at & ~3ull;
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(json + base);
+  const uint32_t a = base + 4 <= n ? __ldg(w) : 0u, b = base + 8 <= n ? __ldg(w + 1) : 0u, c = base + 12 <= n ? __ldg(w + 2) : 0u,
+                 d = base + 16 <= n ? __ldg(w + 3) : 0u;
+  const unsigned sh = (unsigned)(at & 3) * 8;
+  k0 = __funnelshift_r(a, b, sh);
+  k1 = __funnelshift_r(b, c, sh);
+  k2 = __funnelshift_r(c, d, sh);
+}
+__device__ __forceinline__ void copy_text(uint8_t* dst, const uint8_t* __restrict__ src, unsigned long long len) {
+  for (unsigned long long i = 0; i < len; i++) dst[i] = src[i];
+}
+// a backslash strictly between the quotes at p and q?
+__device__ __forceinline__ bool has_escape(const Masks& mk, unsigned long long p, unsigned long long q) {
+  const unsigned long long g0 = p >> 5, g1 = q >> 5;
+  for (unsigned long long gi = g0; gi <= g1; gi++) {
+    uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * gi + 1) + 1);
+    if (gi == g0) w &= ~0u << (unsigned)(p & 31);
+    if (gi == g1) w &= (1u << (unsigned)(q & 31)) - 1u;
+    if (w) return true;
+  }
+  return false;
+}
+
+// What the measuring pass notes down per row entry, so that the writing pass neither walks nor compares
+// again: x = offset of the key (type) text from the start of the element, y = (value text - key text)
+// as int16 | key length << 16 | value length << 24.
+constexpr int kMaxDesc = 16;
+
+// Walk from byte `pos` until the level `top` closes.  top = L_NODE: `pos` is the start of an element of
+// `items`; finds status.capacity / status.conditions (pl), sizes the row and, when `desc` is given, notes
+// the entries down (n_desc < 0: they did not fit the short form).  top = L_CAP or L_CONDS: `pos` is
+// just inside the container (writing pass for rows without descriptors).  One loop; an iteration is one
+// whole member (key, value), one array element, or one group of a container being skipped, so that
+// the lanes of a warp, each somewhere else in its node, run the same code.  False: something the fast
+// walker does not do -- the general parser takes the node.
+__device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n, const Masks& mk, unsigned long long pos, int top,
+                          NodePlan& pl, RowOut& o, uint2* __restrict__ desc, int& n_desc) {
+  const unsigned long long g_end = (n + kGroup - 1) / kGroup;
+  unsigned long long g = pos >> 5;
+  const bool out_of_range = g >= g_end;
+  if (out_of_range) g = g_end ? g_end - 1 : 0;
+  uint32_t so, sc, op, cl, cm;
+  uint4 na = make_uint4(0, 0, 0, 0);  // the next group, fetched ahead
+  uint32_t nk = 0;
+  so = sc = op = cl = cm = 0;
+  if (g_end && top >= 0) {
+    const uint4 a = __ldg(mk.w + 2 * g);
+    const uint32_t keep = ~0u << (unsigned)(pos & 31);
+    so = a.x & keep, sc = a.y & keep, op = a.z & keep, cl = a.w & keep;
+    cm = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * g + 1)) & keep;
+    if (g + 1 < g_end) {
+      na = __ldg(mk.w + 2 * (g + 1));
+      nk = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * (g + 1) + 1));
+    }
+  }
+  bool ended = false;  // ran off the document
+  auto advance = [&]() {
+    if (g + 1 >= g_end) {
+      ended = true;
+      so = sc = op = cl = cm = 0;
+      return;
+    }
+    ++g;
+    so = na.x, sc = na.y, op = na.z, cl = na.w, cm = nk;
+    if (g + 1 < g_end) {
+      na = __ldg(mk.w + 2 * (g + 1));
+      nk = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * (g + 1) + 1));
+    }
+  };
+  // the next structural byte: its kind, its position in `at`; -1 at the end of the document
+  auto next = [&](unsigned long long& at) -> int {
+    uint32_t any;
+    while ((any = so | sc | op | cl | cm) == 0) {
+      advance();
+      if (ended) return -1;
+    }
+    const int bit = __ffs(any) - 1;
+    const uint32_t bm = 1u << bit, keep = ~((bm << 1) - 1u);
+    at = (g << 5) + bit;
+    const int kind = (so & bm) ? SK_STR_OPEN : (sc & bm) ? SK_STR_CLOSE : (op & bm) ? SK_OPEN : (cl & bm) ? SK_CLOSE : SK_COMMA;
+    so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep;
+    return kind;
+  };
+
+  // the opening bracket has just been consumed: pass its container, whole groups at a time where it cannot close
+  auto skip_container = [&]() -> bool {
+    int depth = 1;
+    while (true) {
+      if (__popc(cl) < depth) {
+        depth += __popc(op) - __popc(cl);
+      } else {
+        uint32_t oc = op | cl;
+        while (oc) {
+          const int bit = __ffs(oc) - 1;
+          oc &= oc - 1;
+          if ((op >> bit) & 1u) {
+            depth++;
+          } else if (--depth == 0) {
+            const uint32_t keep = ~((2u << bit) - 1u);
+            so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep;
+            return true;
+          }
+        }
+      }
+      advance();
+      if (ended) return false;
+    }
+  };
+
+  // level L_ITEM: the element itself (a value with no key, like the elements of L_CONDS)
+  int level = top == L_NODE ? L_ITEM : top;
+  bool run = !(out_of_range || top < 0), ok = true;  // top < 0: a lane with no node, along for the votes
+  unsigned long long tp = 0, tl = 0, sp = 0, sl = 0;       // the current condition's type and status text
+  bool seen_status = false, seen_cap = false, seen_cond = false, have_t = false, have_s = false;
+  const unsigned long long node_pos = pos;
+  auto note = [&](unsigned long long ktext, unsigned long long kl, unsigned long long vtext, unsigned long long vl, bool is_cap) {
+    if (!desc || n_desc < 0) return;
+    const long long dlt = vl ? (long long)(vtext - ktext) : 0;
+    const unsigned long long x = kl ? ktext - node_pos : (vl ? vtext - node_pos : 0);
+    const long long d2 = kl ? dlt : 0;  // with no key text the value text sits at x itself
+    if (n_desc >= kMaxDesc || kl >= 255 || vl >= 255 || x > 0xFFFFFFFFull || d2 < -32768 || d2 > 32767 || (is_cap && o.n_cond)) {
+      n_desc = -1;  // too many, too long, too far apart, or conditions written before capacity: walk again when writing
+      return;
+    }
+    desc[n_desc++] = make_uint2((uint32_t)x, (uint32_t)(d2 & 0xFFFF) | (uint32_t)kl << 16 | (uint32_t)vl << 24);
+  };
+  if (out_of_range) ok = false;
+
+  // Every lane of the warp must call this function together.  One iteration = one member of an object
+  // (key and value) or one element of an array, whatever the level: the same code for every lane, and
+  // nodes of the same shape stay in step.  The vote at the top brings the lanes back together once per
+  // iteration (left alone, lanes that took different paths never re-join).
+  while (__any_sync(0xFFFFFFFFu, run)) {
+    if (!run) continue;
+    const bool keyed = level != L_ITEM && level != L_CONDS;
+    unsigned long long at = 0, p = 0, q = 0, q2 = 0;
+    int kind = next(at);
+    if (kind == SK_COMMA && level != L_ITEM) kind = next(at);  // the separator before this member (after the element itself a comma ends it)
+    bool pop = kind == SK_CLOSE;
+    int key = KEY_OTHER;
+    unsigned long long kl = 0;
+    if (!pop && keyed) {
+      // ---- the key ----
+      p = at;
+      if (kind != SK_STR_OPEN || next(q) != SK_STR_CLOSE || has_escape(mk, p, q)) {  // an escaped key could spell one that matters
+        ok = run = false;
+        continue;
+      }
+      kl = q - p - 1;
+      const bool look = level == L_NODE ? kl == 6 : level == L_STATUS ? (kl == 8 || kl == 10) : level == L_COND ? (kl == 4 || kl == 6) : false;
+      if (look) {
+        uint32_t k0, k1, k2;
+        key_words(json, n, p + 1, k0, k1, k2);
+        const bool is_status = kl == 6 && k0 == le4('s', 't', 'a', 't') && (k1 & 0xFFFFu) == le4('u', 's');
+        bool again = false;  // a second member of a name that matters: last one wins, general parser
+        if (level == L_NODE) {
+          if (is_status) key = KEY_A, again = seen_status, seen_status = true;
+        } else if (level == L_STATUS) {
+          if (kl == 8 && k0 == le4('c', 'a', 'p', 'a') && k1 == le4('c', 'i', 't', 'y')) key = KEY_A, again = seen_cap, seen_cap = true;
+          else if (kl == 10 && k0 == le4('c', 'o', 'n', 'd') && k1 == le4('i', 't', 'i', 'o') && (k2 & 0xFFFFu) == le4('n', 's'))
+            key = KEY_B, again = seen_cond, seen_cond = true;
+        } else {
+          if (kl == 4 && k0 == le4('t', 'y', 'p', 'e')) key = KEY_A, again = have_t;
+          else if (is_status) key = KEY_B, again = have_s;
+        }
+        if (again) {
+          ok = run = false;
+          continue;
+        }
+      }
+      kind = next(at);  // the first structural byte of the value
+    }
+    if (!pop) {
+      // ---- the value (or array element): `kind` at `at` is its first structural byte ----
+      const bool need_string = level == L_CAP || (level == L_COND && key != KEY_OTHER);
+      if (kind == SK_STR_OPEN) {
+        if (next(q2) != SK_STR_CLOSE || (need_string && has_escape(mk, at, q2))) {
+          ok = run = false;
+          continue;
+        }
+        const unsigned long long vl = q2 - at - 1;
+        if (level == L_CAP) {
+          note(p + 1, kl, at + 1, vl, true);
+          if (!o.write) {
+            o.n_cap++;
+            o.text += kl + vl;
+            o.maxlen = max(o.maxlen, max(kl, vl));
+          } else {
+            o.table(kl, vl);
+            copy_text(o.row + o.text_off, json + p + 1, kl);
+            copy_text(o.row + o.text_off + kl, json + at + 1, vl);
+            o.text_off += kl + vl;
+          }
+        } else if (level == L_COND && key != KEY_OTHER) {
+          if (key == KEY_A) tp = at + 1, tl = vl, have_t = true;
+          else sp = at + 1, sl = vl, have_s = true;
+        }
+      } else if (need_string || kind < 0) {
+        ok = run = false;  // not a string where a string is read (the general parser knows the rules), or the end of the document
+        continue;
+      } else if (kind == SK_OPEN) {
+        const bool wanted = level == L_ITEM || level == L_CONDS || (level == L_NODE && key == KEY_A) || (level == L_STATUS && key != KEY_OTHER);
+        const int ch = wanted ? json[at] : 0;
+        if (level == L_ITEM && ch == '{') {
+          level = L_NODE;
+        } else if (level == L_NODE && key == KEY_A && ch == '{') {
+          level = L_STATUS, seen_cap = seen_cond = false;
+        } else if (level == L_STATUS && key == KEY_A && ch == '{') {
+          pl.cap_pos = at;
+          level = L_CAP;
+        } else if (level == L_STATUS && key == KEY_B && ch == '[') {
+          pl.cond_pos = at;
+          level = L_CONDS;
+        } else if (level == L_CONDS && ch == '{') {
+          level = L_COND;
+          tp = tl = sp = sl = 0;
+          have_t = have_s = false;
+        } else if (!skip_container()) {  // anything else: passed over (an element that is no object is an empty node / no condition)
+          ok = run = false;
+          continue;
+        } else if (level == L_ITEM) {
+          run = false;  // the element was an array: an empty node
+        }
+      } else if (kind == SK_CLOSE) {  // a number / true / false / null, then the end of the container
+        pop = true;
+      } else if (level == L_ITEM) {
+        run = false;  // a scalar element (its comma): an empty node
+      }
+      if (level == L_ITEM && kind == SK_STR_OPEN) run = false;  // a string element: an empty node
+    }
+    if (pop) {
+      if (level == L_COND) {
+        note(tp, tl, sp, sl, false);
+        if (!o.write) {
+          o.n_cond++;
+          o.text += tl + sl;
+          o.maxlen = max(o.maxlen, max(tl, sl));
+        } else {
+          o.table(tl, sl);
+          copy_text(o.row + o.text_off, json + tp, tl);
+          copy_text(o.row + o.text_off + tl, json + sp, sl);
+          o.text_off += tl + sl;
+        }
+        level = L_CONDS;
+      } else if (level == top || level == L_ITEM) {
+        run = false;  // done (L_ITEM: the items array ended where an element should start -- an empty node)
+      } else if (level == L_STATUS) {
+        level = L_NODE;
+      } else {  // L_CAP, L_CONDS
+        level = L_STATUS;
+      }
+    }
+  }
+  return ok;
+}
+
 // row size in bytes (4-byte padded); bit 31 set when the extended form is needed
-__global__ void measure_rows_kernel(const uint8_t* __restrict__ json, unsigned long long n, const unsigned long long* __restrict__ elem_pos,
-                                    const Work* w, unsigned int* __restrict__ sizes, NodePlan* __restrict__ plans) {
+__global__ void measure_rows_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk,
+                                    const unsigned long long* __restrict__ elem_pos, Work* w, unsigned int* __restrict__ sizes,
+                                    NodePlan* __restrict__ plans, uint2* __restrict__ desc) {
   const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= w->n_nodes) return;
+  const bool have = i < w->n_nodes;
+  if (!__any_sync(0xFFFFFFFFu, have)) return;
   RowOut o{};
   o.write = false;
   NodePlan pl;
-  node_locate(json, min(n, w->items_end), elem_pos[i], pl);
-  node_emit(json, min(n, w->items_end), pl, o);
+  pl.cap_pos = pl.cond_pos = ~0ull;
+  int n_desc = 0;
+  const bool fast_ok = fast_walk(json, n, mk, have ? elem_pos[i] : 0, have ? L_NODE : -1, pl, o, desc + (size_t)kMaxDesc * i, n_desc);  // whole warp
+  if (!have) return;
+  pl.fast = fast_ok ? (n_desc >= 0 ? 2u : 1u) : 0u;
+  if (!pl.fast) {
+    o = RowOut{};
+    o.write = false;
+    node_locate(json, min(n, w->items_end), elem_pos[i], pl);
+    node_emit(json, min(n, w->items_end), pl, o);
+    atomicAdd(&w->general_nodes, 1u);
+  }
   pl.n_cap = (unsigned int)o.n_cap;
   pl.n_cond = (unsigned int)o.n_cond;
   plans[i] = pl;
@@ -671,10 +1109,41 @@ __global__ void strip_flag_kernel(const unsigned int* __restrict__ sizes, unsign
   if (i < n) plain[i] = sizes[i] & 0x7FFFFFFFu;
 }
 
-__global__ void write_rows_kernel(const uint8_t* __restrict__ json, unsigned long long n, const NodePlan* __restrict__ plans,
-                                  const Work* w, const unsigned int* __restrict__ sizes, const unsigned long long* __restrict__ offs,
-                                  const unsigned long long* __restrict__ total, uint8_t* __restrict__ rows, unsigned long long rows_cap,
-                                  uint32_t* __restrict__ row_ptr, long long* __restrict__ info) {
+// `len` document bytes from position `at` to dst: aligned 32-bit loads, funnel-shifted; byte stores.
+__device__ __forceinline__ void copy_from_doc(uint8_t* dst, const uint8_t* __restrict__ json, unsigned long long n, unsigned long long at,
+                                              unsigned int len) {
+  if (len == 0) return;
+  unsigned long long base = at & ~3ull;
+  const unsigned sh = (unsigned)(at & 3) * 8;
+  auto word = [&](unsigned long long b) -> uint32_t {  // the aligned word at b; a word that straddles the end is read bytewise
+    if (b + 4 <= n) return __ldg(reinterpret_cast<const uint32_t*>(json + b));
+    uint32_t v = 0;
+    for (unsigned k = 0; b + k < n; k++) v |= (uint32_t)json[b + k] << (8 * k);
+    return v;
+  };
+  uint32_t prev = word(base);
+  for (unsigned int j = 0; j < len; j += 4) {
+    base += 4;
+    const uint32_t nxt = (sh && j + 4 - (sh >> 3) < len) || (!sh && j + 4 < len) ? word(base) : 0u;
+    const uint32_t v = __funnelshift_r(prev, nxt, sh);
+    prev = nxt;
+    const unsigned int m = min(4u, len - j);
+    dst[j] = (uint8_t)v;
+    if (m > 1) dst[j + 1] = (uint8_t)(v >> 8);
+    if (m > 2) dst[j + 2] = (uint8_t)(v >> 16);
+    if (m > 3) dst[j + 3] = (uint8_t)(v >> 24);
+  }
+}
+
+constexpr int kWriteThreads = 128;
+constexpr unsigned int kWriteStage = 40960;  // bytes of rows a CTA assembles in shared memory before one coalesced copy out
+
+__global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
+    const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const NodePlan* __restrict__ plans, const uint2* __restrict__ desc,
+    const unsigned long long* __restrict__ elem_pos, const Work* w, const unsigned int* __restrict__ sizes,
+    const unsigned long long* __restrict__ offs, const unsigned long long* __restrict__ total, uint8_t* __restrict__ rows,
+    unsigned long long rows_cap, uint32_t* __restrict__ row_ptr, long long* __restrict__ info) {
+  extern __shared__ __align__(16) uint8_t sh[];
   const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned int nn = w->n_nodes;
   const bool fits = *total + 32 <= rows_cap && *total < 0xFFF00000ull;
@@ -684,37 +1153,86 @@ __global__ void write_rows_kernel(const uint8_t* __restrict__ json, unsigned lon
     info[INFO_STATUS] = w->status | (fits ? 0 : ST_ROWS_CAP);
     info[INFO_ITEMS_BEGIN] = (long long)w->items_begin;
     info[INFO_ITEMS_END] = (long long)w->items_end;
+    info[INFO_GENERAL_NODES] = w->general_nodes;
     row_ptr[nn] = fits ? (uint32_t)*total : 0u;
     for (int k = 1; k <= 4; k++) row_ptr[nn + k] = row_ptr[nn];
   }
-  if (i >= nn) return;
+  const unsigned int first = blockIdx.x * blockDim.x;
+  if (first >= nn) return;  // whole CTA
+  const bool have = i < nn;
   if (!fits) {
-    row_ptr[i] = 0;
-    return;
+    if (have) row_ptr[i] = 0;
+    return;  // whole CTA
   }
-  const unsigned long long off = offs[i];
-  row_ptr[i] = (uint32_t)off;
-  const unsigned int bytes = sizes[i] & 0x7FFFFFFFu;
-  uint8_t* row = rows + off;
-  for (unsigned int k = 0; k < bytes; k += 4) *reinterpret_cast<uint32_t*>(row + k) = 0u;   // rows are 4-byte aligned
+  // this CTA's rows are one contiguous piece of the output
+  const unsigned int last = min(nn, first + blockDim.x);
+  const unsigned long long blk_lo = offs[first], blk_hi = last < nn ? offs[last] : *total;
+  const bool staged = blk_hi - blk_lo <= kWriteStage;
+  if (staged) {
+    for (unsigned int k = threadIdx.x * 4; k < (unsigned int)(blk_hi - blk_lo); k += blockDim.x * 4) *reinterpret_cast<uint32_t*>(sh + k) = 0u;
+    __syncthreads();
+  }
+  const unsigned long long off = have ? offs[i] : 0;
+  const unsigned int bytes = have ? sizes[i] & 0x7FFFFFFFu : 0u;
+  uint8_t* row = staged ? sh + (off - blk_lo) : rows + off;
+  NodePlan m;
+  m.cap_pos = m.cond_pos = ~0ull;
+  m.n_cap = m.n_cond = m.fast = 0;
   RowOut o{};
   o.write = true;
   o.row = row;
-  o.ext = (sizes[i] >> 31) != 0;
-  const NodePlan m = plans[i];
-  const unsigned long long ne = (unsigned long long)m.n_cap + m.n_cond;
-  if (o.ext) {
-    row[0] = row[1] = 0xFF;
-    uint32_t a = (uint32_t)m.n_cap, b = (uint32_t)m.n_cond;
-    memcpy(row + 4, &a, 4);
-    memcpy(row + 8, &b, 4);
-    o.text_off = 12 + 8 * ne;
-  } else {
-    row[0] = (uint8_t)m.n_cap;
-    row[1] = (uint8_t)m.n_cond;
-    o.text_off = 2 + 2 * ne;
+  if (have) {
+    row_ptr[i] = (uint32_t)off;
+    if (!staged)
+      for (unsigned int k = 0; k < bytes; k += 4) *reinterpret_cast<uint32_t*>(row + k) = 0u;   // rows are 4-byte aligned
+    o.ext = (sizes[i] >> 31) != 0;
+    m = plans[i];
+    const unsigned long long ne = (unsigned long long)m.n_cap + m.n_cond;
+    if (o.ext) {
+      row[0] = row[1] = 0xFF;
+      uint32_t a = (uint32_t)m.n_cap, b = (uint32_t)m.n_cond;
+      memcpy(row + 4, &a, 4);
+      memcpy(row + 8, &b, 4);
+      o.text_off = 12 + 8 * ne;
+    } else {
+      row[0] = (uint8_t)m.n_cap;
+      row[1] = (uint8_t)m.n_cond;
+      o.text_off = 2 + 2 * ne;
+    }
+    if (m.fast == 2) {  // the measuring pass noted every entry down: table and text straight from the notes
+      const uint2* d = desc + (size_t)kMaxDesc * i;
+      const unsigned long long node_pos = elem_pos[i];
+      unsigned long long text_off = o.text_off;
+      for (unsigned int e = 0; e < (unsigned int)ne; e++) {
+        const uint2 v = d[e];
+        const unsigned int kl = (v.y >> 16) & 0xFFu, vl = v.y >> 24;
+        const long long dlt = (short)(v.y & 0xFFFFu);
+        row[2 + 2 * e] = (uint8_t)kl;
+        row[3 + 2 * e] = (uint8_t)vl;
+        const unsigned long long kt = node_pos + v.x;
+        copy_from_doc(row + text_off, json, n, kt, kl);
+        copy_from_doc(row + text_off + kl, json, n, kl ? kt + dlt : kt, vl);
+        text_off += kl + vl;
+      }
+    } else if (m.fast == 0) {
+      node_emit(json, min(n, w->items_end), m, o);
+    }
   }
-  node_emit(json, min(n, w->items_end), m, o);
+  // rows without notes (too many or too long entries): the index walk again, capacity first, then
+  // conditions -- the same walk as the measuring pass, so it succeeds again.  Whole warps call it.
+  const bool rewalk = have && m.fast == 1;
+  if (__any_sync(0xFFFFFFFFu, rewalk)) {
+    NodePlan unused;
+    int none = -1;
+    const bool cap = rewalk && m.cap_pos != ~0ull, cond = rewalk && m.cond_pos != ~0ull;
+    fast_walk(json, n, mk, cap ? m.cap_pos + 1 : 0, cap ? L_CAP : -1, unused, o, nullptr, none);
+    fast_walk(json, n, mk, cond ? m.cond_pos + 1 : 0, cond ? L_CONDS : -1, unused, o, nullptr, none);
+  }
+  if (staged) {
+    __syncthreads();
+    uint32_t* dst = reinterpret_cast<uint32_t*>(rows + blk_lo);  // row offsets are multiples of 4
+    for (unsigned int k = threadIdx.x; k < (unsigned int)((blk_hi - blk_lo) >> 2); k += blockDim.x) dst[k] = reinterpret_cast<const uint32_t*>(sh)[k];
+  }
 }
 
 }  // namespace js

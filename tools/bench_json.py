@@ -51,5 +51,5 @@ for _ in range(reps):
 s, c = float(np.median(scan_ms)), float(np.median(cls_ms))
 print(json.dumps({"nodes": n, "json_bytes": len(doc), "json_bytes_per_node": len(doc) / n, "scan_ms": s, "classify_ms": c,
                   "scan_GBps": len(doc) / s / 1e6, "nodes_per_s_scan_plus_classify": n / ((s + c) * 1e-3),
-                  "pnl_rows_bytes": batch.rows_bytes, "gpu_nodes": int(out.counts[0]),
+                  "pnl_rows_bytes": batch.rows_bytes, "general_parser_nodes": int(info[5]), "gpu_nodes": int(out.counts[0]),
                   "host_json_loads_s": t_loads, "host_json_loads_MBps": len(doc) / t_loads / 1e6}))
