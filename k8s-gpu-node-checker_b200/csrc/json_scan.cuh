@@ -828,18 +828,6 @@ __device__ __forceinline__ void key_words(const uint8_t* __restrict__ json, unsi
 __device__ __forceinline__ void copy_text(uint8_t* dst, const uint8_t* __restrict__ src, unsigned long long len) {
   for (unsigned long long i = 0; i < len; i++) dst[i] = src[i];
 }
-// a backslash strictly between the quotes at p and q?
-__device__ __forceinline__ bool has_escape(const Masks& mk, unsigned long long p, unsigned long long q) {
-  const unsigned long long g0 = p >> 5, g1 = q >> 5;
-  for (unsigned long long gi = g0; gi <= g1; gi++) {
-    uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * gi + 1) + 1);
-    if (gi == g0) w &= ~0u << (unsigned)(p & 31);
-    if (gi == g1) w &= (1u << (unsigned)(q & 31)) - 1u;
-    if (w) return true;
-  }
-  return false;
-}
-
 // What the measuring pass notes down per row entry, so that the writing pass neither walks nor compares
 // again: x = offset of the key (type) text from the start of the element, y = (value text - key text)
 // as int16 | key length << 16 | value length << 24.
@@ -848,46 +836,54 @@ constexpr int kMaxDesc = 16;
 // Walk from byte `pos` until the level `top` closes.  top = L_NODE: `pos` is the start of an element of
 // `items`; finds status.capacity / status.conditions (pl), sizes the row and, when `desc` is given, notes
 // the entries down (n_desc < 0: they did not fit the short form).  top = L_CAP or L_CONDS: `pos` is
-// just inside the container (writing pass for rows without descriptors).  One loop; an iteration is one
-// whole member (key, value), one array element, or one group of a container being skipped, so that
-// the lanes of a warp, each somewhere else in its node, run the same code.  False: something the fast
-// walker does not do -- the general parser takes the node.
+// just inside the container (writing pass for rows without notes).  top < 0: a lane with no node,
+// along for the votes.  False: something the fast walker does not do -- the general parser takes the node.
+//
+// Every lane of the warp must call this function together.  One iteration = one member of an object
+// (key and value) or one element of an array, whatever the level: the same code for every lane, and
+// nodes of the same shape stay in step.  The vote at the top brings the lanes back together once per
+// iteration (left alone, lanes that took different paths never re-join and the warp runs at a handful
+// of active lanes).  Positions inside are 32-bit, relative to the 32-byte group the walk starts in.
 __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n, const Masks& mk, unsigned long long pos, int top,
                           NodePlan& pl, RowOut& o, uint2* __restrict__ desc, int& n_desc) {
-  const unsigned long long g_end = (n + kGroup - 1) / kGroup;
-  unsigned long long g = pos >> 5;
-  const bool out_of_range = g >= g_end;
-  if (out_of_range) g = g_end ? g_end - 1 : 0;
-  uint32_t so, sc, op, cl, cm;
-  uint4 na = make_uint4(0, 0, 0, 0);  // the next group, fetched ahead
-  uint32_t nk = 0;
-  so = sc = op = cl = cm = 0;
-  if (g_end && top >= 0) {
-    const uint4 a = __ldg(mk.w + 2 * g);
-    const uint32_t keep = ~0u << (unsigned)(pos & 31);
-    so = a.x & keep, sc = a.y & keep, op = a.z & keep, cl = a.w & keep;
-    cm = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * g + 1)) & keep;
-    if (g + 1 < g_end) {
-      na = __ldg(mk.w + 2 * (g + 1));
-      nk = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * (g + 1) + 1));
+  const unsigned long long g_end = (n + kGroup - 1) / kGroup, g0 = pos >> 5;
+  const bool idle = g0 >= g_end || top < 0;
+  const unsigned long long base0 = g0 << 5;               // document position of relative position 0
+  const uint32_t rel0 = (uint32_t)(pos & 31);             // relative position of the start of the walk
+  const uint4* wp = mk.w + (idle ? 0 : 2 * g0);           // the current group's masks
+  uint32_t left = idle ? 0u : (uint32_t)min(g_end - g0 - 1, 0x03FFFFFFull);  // groups that may still follow (2 GiB per walk)
+  uint32_t gr = 0;                                        // current group, relative
+  uint32_t so = 0, sc = 0, op = 0, cl = 0, cm = 0, bk = 0;
+  uint4 na = make_uint4(0, 0, 0, 0);                      // the next group, fetched ahead
+  uint2 nb = make_uint2(0, 0);
+  if (!idle) {
+    const uint4 a = __ldg(wp);
+    const uint2 b = __ldg(reinterpret_cast<const uint2*>(wp + 1));
+    const uint32_t keep = ~0u << rel0;
+    so = a.x & keep, sc = a.y & keep, op = a.z & keep, cl = a.w & keep, cm = b.x & keep, bk = b.y & keep;
+    if (left) {
+      na = __ldg(wp + 2);
+      nb = __ldg(reinterpret_cast<const uint2*>(wp + 3));
     }
   }
-  bool ended = false;  // ran off the document
+  bool ended = false;   // ran off the document
+  uint32_t bacc = 0;    // backslashes passed since the last opening quote
   auto advance = [&]() {
-    if (g + 1 >= g_end) {
+    if (left == 0) {
       ended = true;
-      so = sc = op = cl = cm = 0;
+      so = sc = op = cl = cm = bk = 0;
       return;
     }
-    ++g;
-    so = na.x, sc = na.y, op = na.z, cl = na.w, cm = nk;
-    if (g + 1 < g_end) {
-      na = __ldg(mk.w + 2 * (g + 1));
-      nk = __ldg(reinterpret_cast<const uint32_t*>(mk.w + 2 * (g + 1) + 1));
+    --left, ++gr, wp += 2;
+    bacc |= bk;
+    so = na.x, sc = na.y, op = na.z, cl = na.w, cm = nb.x, bk = nb.y;
+    if (left) {
+      na = __ldg(wp + 2);
+      nb = __ldg(reinterpret_cast<const uint2*>(wp + 3));
     }
   };
-  // the next structural byte: its kind, its position in `at`; -1 at the end of the document
-  auto next = [&](unsigned long long& at) -> int {
+  // the next structural byte: its kind, its relative position in `at`; -1 at the end of the document
+  auto next = [&](uint32_t& at) -> int {
     uint32_t any;
     while ((any = so | sc | op | cl | cm) == 0) {
       advance();
@@ -895,12 +891,12 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
     }
     const int bit = __ffs(any) - 1;
     const uint32_t bm = 1u << bit, keep = ~((bm << 1) - 1u);
-    at = (g << 5) + bit;
+    at = (gr << 5) + bit;
     const int kind = (so & bm) ? SK_STR_OPEN : (sc & bm) ? SK_STR_CLOSE : (op & bm) ? SK_OPEN : (cl & bm) ? SK_CLOSE : SK_COMMA;
-    so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep;
+    bacc = kind == SK_STR_OPEN ? 0u : (bacc | (bk & ~keep));  // at a closing quote: non-zero iff the string held a backslash
+    so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep, bk &= keep;
     return kind;
   };
-
   // the opening bracket has just been consumed: pass its container, whole groups at a time where it cannot close
   auto skip_container = [&]() -> bool {
     int depth = 1;
@@ -916,7 +912,7 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
             depth++;
           } else if (--depth == 0) {
             const uint32_t keep = ~((2u << bit) - 1u);
-            so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep;
+            so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep, bk &= keep;
             return true;
           }
         }
@@ -928,40 +924,45 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
 
   // level L_ITEM: the element itself (a value with no key, like the elements of L_CONDS)
   int level = top == L_NODE ? L_ITEM : top;
-  bool run = !(out_of_range || top < 0), ok = true;  // top < 0: a lane with no node, along for the votes
-  unsigned long long tp = 0, tl = 0, sp = 0, sl = 0;       // the current condition's type and status text
+  bool run = !idle, ok = !idle;
+  uint32_t tp = 0, tl = 0, sp = 0, sl = 0;                 // the current condition's type and status text (relative)
+  uint32_t n_cap = 0, n_cond = 0, text = 0, maxlen = 0;    // what the measuring pass wants to know
   bool seen_status = false, seen_cap = false, seen_cond = false, have_t = false, have_s = false;
-  const unsigned long long node_pos = pos;
-  auto note = [&](unsigned long long ktext, unsigned long long kl, unsigned long long vtext, unsigned long long vl, bool is_cap) {
-    if (!desc || n_desc < 0) return;
-    const long long dlt = vl ? (long long)(vtext - ktext) : 0;
-    const unsigned long long x = kl ? ktext - node_pos : (vl ? vtext - node_pos : 0);
-    const long long d2 = kl ? dlt : 0;  // with no key text the value text sits at x itself
-    if (n_desc >= kMaxDesc || kl >= 255 || vl >= 255 || x > 0xFFFFFFFFull || d2 < -32768 || d2 > 32767 || (is_cap && o.n_cond)) {
-      n_desc = -1;  // too many, too long, too far apart, or conditions written before capacity: walk again when writing
+  // one row entry: key text (kt, kl) and value text (vt, vl), relative positions
+  auto entry = [&](uint32_t kt, uint32_t kl, uint32_t vt, uint32_t vl, bool is_cap) {
+    if (o.write) {
+      o.table(kl, vl);
+      copy_text(o.row + o.text_off, json + base0 + kt, kl);
+      copy_text(o.row + o.text_off + kl, json + base0 + vt, vl);
+      o.text_off += kl + vl;
       return;
     }
-    desc[n_desc++] = make_uint2((uint32_t)x, (uint32_t)(d2 & 0xFFFF) | (uint32_t)kl << 16 | (uint32_t)vl << 24);
+    if (desc && n_desc >= 0) {
+      const uint32_t x = (kl ? kt : vl ? vt : rel0) - rel0;
+      const int d = kl && vl ? (int)(vt - kt) : 0;  // with no key text the value text sits at x itself
+      if (n_desc >= kMaxDesc || kl >= 255 || vl >= 255 || d < -32768 || d > 32767 || (is_cap && n_cond))
+        n_desc = -1;  // too many, too long, too far apart, or conditions seen before capacity: walk again when writing
+      else
+        desc[n_desc++] = make_uint2(x, (uint32_t)(d & 0xFFFF) | kl << 16 | vl << 24);
+    }
+    if (is_cap) n_cap++;
+    else n_cond++;
+    text += kl + vl;
+    maxlen = max(maxlen, max(kl, vl));
   };
-  if (out_of_range) ok = false;
 
-  // Every lane of the warp must call this function together.  One iteration = one member of an object
-  // (key and value) or one element of an array, whatever the level: the same code for every lane, and
-  // nodes of the same shape stay in step.  The vote at the top brings the lanes back together once per
-  // iteration (left alone, lanes that took different paths never re-join).
   while (__any_sync(0xFFFFFFFFu, run)) {
     if (!run) continue;
     const bool keyed = level != L_ITEM && level != L_CONDS;
-    unsigned long long at = 0, p = 0, q = 0, q2 = 0;
+    uint32_t at = 0, p = 0, q = 0, q2 = 0, kl = 0;
     int kind = next(at);
     if (kind == SK_COMMA && level != L_ITEM) kind = next(at);  // the separator before this member (after the element itself a comma ends it)
     bool pop = kind == SK_CLOSE;
     int key = KEY_OTHER;
-    unsigned long long kl = 0;
     if (!pop && keyed) {
       // ---- the key ----
       p = at;
-      if (kind != SK_STR_OPEN || next(q) != SK_STR_CLOSE || has_escape(mk, p, q)) {  // an escaped key could spell one that matters
+      if (kind != SK_STR_OPEN || next(q) != SK_STR_CLOSE || bacc) {  // an escaped key could spell one that matters
         ok = run = false;
         continue;
       }
@@ -969,7 +970,7 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
       const bool look = level == L_NODE ? kl == 6 : level == L_STATUS ? (kl == 8 || kl == 10) : level == L_COND ? (kl == 4 || kl == 6) : false;
       if (look) {
         uint32_t k0, k1, k2;
-        key_words(json, n, p + 1, k0, k1, k2);
+        key_words(json, n, base0 + p + 1, k0, k1, k2);
         const bool is_status = kl == 6 && k0 == le4('s', 't', 'a', 't') && (k1 & 0xFFFFu) == le4('u', 's');
         bool again = false;  // a second member of a name that matters: last one wins, general parser
         if (level == L_NODE) {
@@ -993,42 +994,34 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
       // ---- the value (or array element): `kind` at `at` is its first structural byte ----
       const bool need_string = level == L_CAP || (level == L_COND && key != KEY_OTHER);
       if (kind == SK_STR_OPEN) {
-        if (next(q2) != SK_STR_CLOSE || (need_string && has_escape(mk, at, q2))) {
+        if (next(q2) != SK_STR_CLOSE || (need_string && bacc)) {
           ok = run = false;
           continue;
         }
-        const unsigned long long vl = q2 - at - 1;
+        const uint32_t vl = q2 - at - 1;
         if (level == L_CAP) {
-          note(p + 1, kl, at + 1, vl, true);
-          if (!o.write) {
-            o.n_cap++;
-            o.text += kl + vl;
-            o.maxlen = max(o.maxlen, max(kl, vl));
-          } else {
-            o.table(kl, vl);
-            copy_text(o.row + o.text_off, json + p + 1, kl);
-            copy_text(o.row + o.text_off + kl, json + at + 1, vl);
-            o.text_off += kl + vl;
-          }
+          entry(p + 1, kl, at + 1, vl, true);
         } else if (level == L_COND && key != KEY_OTHER) {
           if (key == KEY_A) tp = at + 1, tl = vl, have_t = true;
           else sp = at + 1, sl = vl, have_s = true;
+        } else if (level == L_ITEM) {
+          run = false;  // a string element: an empty node
         }
       } else if (need_string || kind < 0) {
         ok = run = false;  // not a string where a string is read (the general parser knows the rules), or the end of the document
         continue;
       } else if (kind == SK_OPEN) {
         const bool wanted = level == L_ITEM || level == L_CONDS || (level == L_NODE && key == KEY_A) || (level == L_STATUS && key != KEY_OTHER);
-        const int ch = wanted ? json[at] : 0;
+        const int ch = wanted ? json[base0 + at] : 0;
         if (level == L_ITEM && ch == '{') {
           level = L_NODE;
         } else if (level == L_NODE && key == KEY_A && ch == '{') {
           level = L_STATUS, seen_cap = seen_cond = false;
         } else if (level == L_STATUS && key == KEY_A && ch == '{') {
-          pl.cap_pos = at;
+          pl.cap_pos = base0 + at;
           level = L_CAP;
         } else if (level == L_STATUS && key == KEY_B && ch == '[') {
-          pl.cond_pos = at;
+          pl.cond_pos = base0 + at;
           level = L_CONDS;
         } else if (level == L_CONDS && ch == '{') {
           level = L_COND;
@@ -1045,21 +1038,10 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
       } else if (level == L_ITEM) {
         run = false;  // a scalar element (its comma): an empty node
       }
-      if (level == L_ITEM && kind == SK_STR_OPEN) run = false;  // a string element: an empty node
     }
     if (pop) {
       if (level == L_COND) {
-        note(tp, tl, sp, sl, false);
-        if (!o.write) {
-          o.n_cond++;
-          o.text += tl + sl;
-          o.maxlen = max(o.maxlen, max(tl, sl));
-        } else {
-          o.table(tl, sl);
-          copy_text(o.row + o.text_off, json + tp, tl);
-          copy_text(o.row + o.text_off + tl, json + sp, sl);
-          o.text_off += tl + sl;
-        }
+        entry(tp, tl, sp, sl, false);
         level = L_CONDS;
       } else if (level == top || level == L_ITEM) {
         run = false;  // done (L_ITEM: the items array ended where an element should start -- an empty node)
@@ -1070,6 +1052,7 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
       }
     }
   }
+  if (!o.write) o.n_cap += n_cap, o.n_cond += n_cond, o.text += text, o.maxlen = max(o.maxlen, (unsigned long long)maxlen);
   return ok;
 }
 
