@@ -1107,7 +1107,8 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
     c->launches += 2;
   }
   if ((rc = device_exclusive_scan<unsigned long long, OpAddULL>(c, plain, nodes_cap, offs, bt64, total, OpAddULL(), 0ull, stream))) return rc;
-  write_rows_kernel<<<nb, kWriteThreads, kWriteStage, stream>>>(json, n, mk, plans, desc, elem, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
+  CUDA_TRY(c, cudaFuncSetAttribute(write_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWriteSmem));
+  write_rows_kernel<<<nb, kWriteThreads, kWriteSmem, stream>>>(json, n, mk, plans, desc, elem, work, sizes, offs, total, out->rows, out->rows_cap, out->row_ptr, (long long*)out->info);
   CUDA_TRY(c, cudaGetLastError());
   c->launches += 1;
   return GNC_OK;

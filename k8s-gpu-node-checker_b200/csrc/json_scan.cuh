@@ -1119,15 +1119,33 @@ __device__ __forceinline__ void copy_from_doc(uint8_t* dst, const uint8_t* __res
 }
 
 constexpr int kWriteThreads = 128;
-constexpr unsigned int kWriteStage = 40960;  // bytes of rows a CTA assembles in shared memory before one coalesced copy out
+constexpr unsigned int kWriteStage = 32768;   // bytes of rows a CTA assembles in shared memory before one coalesced copy out
+constexpr unsigned int kSpan = 1280;          // bytes of document one node's texts may span to be gathered by the whole warp
+constexpr int kGatherBatch = 4;               // nodes whose spans a warp holds in shared memory at a time (8 lanes cut each node's row)
+constexpr unsigned int kWriteSmem = kWriteStage + (kWriteThreads / 32) * kGatherBatch * kSpan + kWriteThreads * (8 + 4 + 4 + 4 + 8) +
+                                    kMaxDesc * kWriteThreads * 8;
 
+// Writing pass.  A CTA's rows are one contiguous piece of the output: they are assembled in shared memory and
+// copied out coalesced.  The texts of a node (capacity keys and values, condition types and statuses)
+// lie within about a kilobyte of the document; the measuring pass noted where.  A thread fetching its own
+// node's texts one after another waits a memory round trip for each, so the warp fetches them together:
+// for eight nodes at a time all 32 lanes copy the nodes' spans into shared memory with independent 16-byte
+// loads, then the eight owning lanes cut their rows out of shared memory.
 __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
     const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const NodePlan* __restrict__ plans, const uint2* __restrict__ desc,
     const unsigned long long* __restrict__ elem_pos, const Work* w, const unsigned int* __restrict__ sizes,
     const unsigned long long* __restrict__ offs, const unsigned long long* __restrict__ total, uint8_t* __restrict__ rows,
     unsigned long long rows_cap, uint32_t* __restrict__ row_ptr, long long* __restrict__ info) {
   extern __shared__ __align__(16) uint8_t sh[];
+  uint8_t* gather = sh + kWriteStage;                                                    // [warps][kGatherBatch][kSpan]
+  unsigned long long* s_lo = reinterpret_cast<unsigned long long*>(gather + (kWriteThreads / 32) * kGatherBatch * kSpan);  // [threads] span start
+  uint8_t** s_rowp = reinterpret_cast<uint8_t**>(s_lo + kWriteThreads);                    // [threads] where the row is assembled
+  uint2* s_desc = reinterpret_cast<uint2*>(s_rowp + kWriteThreads);                        // [kMaxDesc][threads] the notes
+  unsigned int* s_len = reinterpret_cast<unsigned int*>(s_desc + kMaxDesc * kWriteThreads);  // [threads] span length, 0: not gathered
+  int* s_shift = reinterpret_cast<int*>(s_len + kWriteThreads);                            // [threads] node start - span start
+  unsigned int* s_ne = reinterpret_cast<unsigned int*>(s_shift + kWriteThreads);           // [threads] entries
   const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned int nn = w->n_nodes;
   const bool fits = *total + 32 <= rows_cap && *total < 0xFFF00000ull;
   if (i == 0) {
@@ -1147,7 +1165,6 @@ __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
     if (have) row_ptr[i] = 0;
     return;  // whole CTA
   }
-  // this CTA's rows are one contiguous piece of the output
   const unsigned int last = min(nn, first + blockDim.x);
   const unsigned long long blk_lo = offs[first], blk_hi = last < nn ? offs[last] : *total;
   const bool staged = blk_hi - blk_lo <= kWriteStage;
@@ -1164,43 +1181,127 @@ __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
   RowOut o{};
   o.write = true;
   o.row = row;
+  unsigned int ne = 0;
   if (have) {
     row_ptr[i] = (uint32_t)off;
     if (!staged)
       for (unsigned int k = 0; k < bytes; k += 4) *reinterpret_cast<uint32_t*>(row + k) = 0u;   // rows are 4-byte aligned
     o.ext = (sizes[i] >> 31) != 0;
     m = plans[i];
-    const unsigned long long ne = (unsigned long long)m.n_cap + m.n_cond;
+    ne = m.n_cap + m.n_cond;
     if (o.ext) {
       row[0] = row[1] = 0xFF;
       uint32_t a = (uint32_t)m.n_cap, b = (uint32_t)m.n_cond;
       memcpy(row + 4, &a, 4);
       memcpy(row + 8, &b, 4);
-      o.text_off = 12 + 8 * ne;
+      o.text_off = 12 + 8 * (unsigned long long)ne;
     } else {
       row[0] = (uint8_t)m.n_cap;
       row[1] = (uint8_t)m.n_cond;
-      o.text_off = 2 + 2 * ne;
-    }
-    if (m.fast == 2) {  // the measuring pass noted every entry down: table and text straight from the notes
-      const uint2* d = desc + (size_t)kMaxDesc * i;
-      const unsigned long long node_pos = elem_pos[i];
-      unsigned long long text_off = o.text_off;
-      for (unsigned int e = 0; e < (unsigned int)ne; e++) {
-        const uint2 v = d[e];
-        const unsigned int kl = (v.y >> 16) & 0xFFu, vl = v.y >> 24;
-        const long long dlt = (short)(v.y & 0xFFFFu);
-        row[2 + 2 * e] = (uint8_t)kl;
-        row[3 + 2 * e] = (uint8_t)vl;
-        const unsigned long long kt = node_pos + v.x;
-        copy_from_doc(row + text_off, json, n, kt, kl);
-        copy_from_doc(row + text_off + kl, json, n, kl ? kt + dlt : kt, vl);
-        text_off += kl + vl;
-      }
-    } else if (m.fast == 0) {
-      node_emit(json, min(n, w->items_end), m, o);
+      o.text_off = 2 + 2 * (unsigned long long)ne;
     }
   }
+  // ---- rows with notes (fast == 2: at most kMaxDesc entries, short form) ----
+  const bool noted = have && m.fast == 2;
+  uint2 d[kMaxDesc];
+  unsigned int lo = 0xFFFFFFFFu, hi = 0;  // the node's texts lie in [node_pos + lo, node_pos + hi)
+#pragma unroll
+  for (int e = 0; e < kMaxDesc; e++) {
+    d[e] = make_uint2(0, 0);
+    if (noted && (unsigned int)e < ne) {
+      d[e] = __ldg(desc + (size_t)kMaxDesc * i + e);
+      const unsigned int kl = (d[e].y >> 16) & 0xFFu, vl = d[e].y >> 24;
+      const unsigned int vt = kl ? d[e].x + (int)(short)(d[e].y & 0xFFFFu) : d[e].x;
+      if (kl) lo = min(lo, d[e].x), hi = max(hi, d[e].x + kl);
+      if (vl) lo = min(lo, vt), hi = max(hi, vt + vl);
+    }
+  }
+  const unsigned long long node_pos = have ? elem_pos[i] : 0;
+  const unsigned long long span_lo = (node_pos + (lo <= hi ? lo : 0)) & ~15ull;          // 16-byte aligned document position
+  const unsigned int span_len = lo < hi ? (unsigned int)(node_pos + hi - span_lo) : 0u;
+  const bool gathered = noted && span_len <= kSpan;
+  s_lo[threadIdx.x] = span_lo;
+  s_len[threadIdx.x] = gathered ? span_len : 0u;
+  s_shift[threadIdx.x] = (int)(long long)(node_pos - span_lo);
+  s_rowp[threadIdx.x] = row;
+  s_ne[threadIdx.x] = gathered ? ne : 0u;
+#pragma unroll
+  for (int e = 0; e < kMaxDesc; e++) s_desc[e * kWriteThreads + threadIdx.x] = d[e];
+  __syncwarp();
+  uint8_t* wbuf = gather + warp * (kGatherBatch * kSpan);
+  auto load16 = [&](unsigned long long at) -> uint4 {
+    if (at + 16 <= n) return __ldg(reinterpret_cast<const uint4*>(json + at));
+    uint8_t tmp[16];
+    for (int t = 0; t < 16; t++) tmp[t] = at + t < n ? json[at + t] : (uint8_t)0;
+    uint4 v;
+    memcpy(&v, tmp, 16);
+    return v;
+  };
+  for (int b0 = 0; b0 < 32; b0 += kGatherBatch) {
+    // every load of the batch is issued before the first store waits for one
+    uint4 v[kGatherBatch][2];
+    unsigned int jlen[kGatherBatch];
+#pragma unroll
+    for (int j = 0; j < kGatherBatch; j++) {
+      const unsigned long long jlo = s_lo[warp * 32 + b0 + j];
+      jlen[j] = s_len[warp * 32 + b0 + j];
+      const unsigned int k0 = lane * 16, k1 = k0 + 512;
+      v[j][0] = v[j][1] = make_uint4(0, 0, 0, 0);
+      if (k0 < jlen[j]) v[j][0] = load16(jlo + k0);
+      if (k1 < jlen[j]) v[j][1] = load16(jlo + k1);
+    }
+#pragma unroll
+    for (int j = 0; j < kGatherBatch; j++) {
+      const unsigned int k0 = lane * 16, k1 = k0 + 512, k2 = k0 + 1024;
+      if (k0 < jlen[j]) *reinterpret_cast<uint4*>(wbuf + j * kSpan + k0) = v[j][0];
+      if (k1 < jlen[j]) *reinterpret_cast<uint4*>(wbuf + j * kSpan + k1) = v[j][1];
+      if (k2 < jlen[j]) *reinterpret_cast<uint4*>(wbuf + j * kSpan + k2) = load16(s_lo[warp * 32 + b0 + j] + k2);  // spans past 1 KB: rare
+    }
+    __syncwarp();
+    {
+      // eight lanes per node: lane q of them writes entries q and q + 8
+      const int j = lane >> 3, q = lane & 7, node = warp * 32 + b0 + j;
+      const unsigned int ne_j = s_ne[node];
+      if (ne_j) {
+        uint8_t* rowp = s_rowp[node];
+        const uint8_t* src = wbuf + j * kSpan + s_shift[node];  // src[x] = document byte (node start + x)
+        unsigned int run = 2 + 2 * ne_j, off_a = 0, off_b = 0;  // where my entries' texts go
+        uint2 da = make_uint2(0, 0), db = make_uint2(0, 0);
+        for (unsigned int e = 0; e < ne_j; e++) {
+          const uint2 de = s_desc[e * kWriteThreads + node];
+          if (e == (unsigned int)q) da = de, off_a = run;
+          if (e == (unsigned int)q + 8) db = de, off_b = run;
+          run += ((de.y >> 16) & 0xFFu) + (de.y >> 24);
+        }
+        auto put = [&](unsigned int e, uint2 de, unsigned int text_off) {
+          const unsigned int kl = (de.y >> 16) & 0xFFu, vl = de.y >> 24;
+          const unsigned int vt = kl ? de.x + (int)(short)(de.y & 0xFFFFu) : de.x;
+          rowp[2 + 2 * e] = (uint8_t)kl;
+          rowp[3 + 2 * e] = (uint8_t)vl;
+          for (unsigned int t = 0; t < kl; t++) rowp[text_off + t] = src[de.x + t];
+          for (unsigned int t = 0; t < vl; t++) rowp[text_off + kl + t] = src[vt + t];
+        };
+        if ((unsigned int)q < ne_j) put(q, da, off_a);
+        if ((unsigned int)q + 8 < ne_j) put(q + 8, db, off_b);
+      }
+    }
+    __syncwarp();
+  }
+  if (noted && !gathered) {  // texts spread too far apart: fetched by the owning thread
+    unsigned long long text_off = o.text_off;
+    for (unsigned int e = 0; e < ne; e++) {
+      const uint2 de = __ldg(desc + (size_t)kMaxDesc * i + e);
+      const unsigned int kl = (de.y >> 16) & 0xFFu, vl = de.y >> 24;
+      const long long dlt = (short)(de.y & 0xFFFFu);
+      row[2 + 2 * e] = (uint8_t)kl;
+      row[3 + 2 * e] = (uint8_t)vl;
+      const unsigned long long kt = node_pos + de.x;
+      copy_from_doc(row + text_off, json, n, kt, kl);
+      copy_from_doc(row + text_off + kl, json, n, kl ? kt + dlt : kt, vl);
+      text_off += kl + vl;
+    }
+  }
+  if (have && m.fast == 0) node_emit(json, min(n, w->items_end), m, o);
   // rows without notes (too many or too long entries): the index walk again, capacity first, then
   // conditions -- the same walk as the measuring pass, so it succeeds again.  Whole warps call it.
   const bool rewalk = have && m.fast == 1;

@@ -1,6 +1,6 @@
 """Aggregate an ncu SASS source page by CUDA source line.
 
-    python tools/ncu_by_line.py <report.ncu-rep> <libgnc.so> [kernel-substring]
+    python tools/ncu_by_line.py <report.ncu-rep> <libgnc.so> [kernel-substring [ncu-kernel-regex]]
 
 ncu's CSV source page is per SASS instruction; nvdisasm -g gives the file:line of each SASS
 instruction of the same cubin.  Both list the kernel's instructions in address order, so they are
@@ -40,7 +40,8 @@ def sass_lines(so, kernel_sub):
 def main():
     rep, so = sys.argv[1], sys.argv[2]
     ksub = sys.argv[3] if len(sys.argv) > 3 else "classify_kernelILi224"
-    csvtxt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    kfilter = ["-k", "regex:" + sys.argv[4]] if len(sys.argv) > 4 else []   # reports holding several kernels: pick one
+    csvtxt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + kfilter, capture_output=True, text=True).stdout
     rows = list(csv.reader(csvtxt.splitlines()))
     hdr = rows[1]
     ix = {h: i for i, h in enumerate(hdr)}
