@@ -1057,7 +1057,7 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
                o_delta = take(n_chunks * 4), o_depth = take(n_chunks * 4), o_bt32 = take(nbc * 4), o_evc = take(n_chunks * 4),
                o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
                o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8),
-               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
+               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_evpack = take(n_chunks * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
   if (off > c->json_scratch_bytes) {
     if (c->json_scratch) {
       CUDA_TRY(c, cudaStreamSynchronize(stream));
@@ -1081,6 +1081,7 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   Masks mk;
   mk.w = (uint4*)(base + o_masks);
   int* min_rel = (int*)(base + o_minrel);
+  unsigned int* evpack = (unsigned int*)(base + o_evpack);
   uint2* desc = (uint2*)(base + o_desc);
   if (!aligned16(json)) return fail(c, GNC_ERR_ARG, "json must be 16-byte aligned");
   CUDA_TRY(c, cudaMemsetAsync(work, 0, sizeof(Work), stream));
@@ -1093,10 +1094,10 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
     if ((rc = device_exclusive_scan<uint8_t, OpCompose>(c, funcs, n_chunks, pf, bt8, nullptr, OpCompose(), (uint8_t)kIdentity, stream))) return rc;
     index_kernel<<<tb, kTileChunks, kTileSmem, stream>>>(json, n, pf, mk, delta, min_rel, n_chunks);
     if ((rc = device_exclusive_scan<int, OpAddI>(c, delta, n_chunks, depth0, bt32, nullptr, OpAddI(), 0, stream))) return rc;
-    events_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, min_rel, evc, work, n_chunks);
+    events_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, min_rel, evc, evpack, work, n_chunks);
     if ((rc = device_exclusive_scan<unsigned int, OpAddU>(c, evc, n_chunks, evp, btu, nullptr, OpAddU(), 0u, stream))) return rc;
     pick_items_kernel<<<1, 1, 0, stream>>>(json, n, mk, depth0, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
-    element_starts_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, evp, work, elem, n_chunks);
+    element_starts_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, evc, evpack, evp, work, elem, n_chunks);
     c->launches += 5;
   }
   const unsigned nb = (unsigned)std::max<unsigned long long>(1, (nodes_cap + 127) / 128);

@@ -274,6 +274,8 @@ struct OpAddULL {
 // Visit, in order, the brackets and commas outside strings of chunk c that lie before `limit`:
 // f(pos, kind, depth_before) with kind 0 open, 1 close, 2 comma.  Groups that stay deeper than the root
 // levels are passed over by popcount.  Returns the depth after the last byte visited.
+// (Stepping bracket to bracket and looking at commas only in stretches at depth 2 was slower: more
+// branches for the same few bits.)
 template <class F>
 __device__ __forceinline__ int visit_structurals(const Masks& mk, unsigned long long c, int depth, unsigned long long limit, F&& f) {
   const uint4* pw = mk.w + c * (2 * kGroupsPerChunk);
@@ -318,22 +320,26 @@ __device__ __forceinline__ int visit_structurals(const Masks& mk, unsigned long 
 
 // events: the '[' of every root-level array and every ',' directly inside one (depth 2 outside strings)
 __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
-                              const int* __restrict__ min_rel, unsigned int* __restrict__ ev_count, Work* w, unsigned long long n_chunks) {
+                              const int* __restrict__ min_rel, unsigned int* __restrict__ ev_count, unsigned int* __restrict__ ev_pack,
+                              Work* w, unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
   if (c >= n_chunks) return;
-  unsigned int cnt = 0;
+  unsigned int cnt = 0, pack = 0;  // pack: where in the chunk the first four events are (element_starts_kernel reads it)
   if (depth0[c] + min_rel[c] > 2) {  // the whole chunk lies deeper than the root levels
     ev_count[c] = 0;
     return;
   }
+  const unsigned long long chunk_base = c * kChunk;
   visit_structurals(mk, c, depth0[c], ~0ull, [&](unsigned long long pos, int kind, int d) {
     if (kind == 0 && d == 1) {
       if (json[pos] == '[') {
+        if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
         cnt++;
         const unsigned int k = atomicAdd(&w->n_open, 1u);
         if (k < kMaxRootArrays) w->root_open[k] = pos;
       }
     } else if (kind == 2 && d == 2) {
+      if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
       cnt++;
     } else if (kind == 1 && d == 2) {
       if (json[pos] == ']') {
@@ -345,6 +351,7 @@ __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, const 
     }
   });
   ev_count[c] = cnt;
+  ev_pack[c] = pack;
 }
 
 // number of events strictly before byte `pos` (pos lies outside strings)
@@ -410,14 +417,22 @@ __global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned lon
 
 // position of the byte after each element's separator
 __global__ void element_starts_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
+                                      const unsigned int* __restrict__ ev_count, const unsigned int* __restrict__ ev_pack,
                                       const unsigned int* __restrict__ ev_prefix, const Work* w,
                                       unsigned long long* __restrict__ elem_pos, unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
   if (c >= n_chunks) return;
+  const unsigned int cnt = ev_count[c];
+  if (cnt == 0) return;
   const unsigned long long lo = w->ev_base, hi = lo + w->n_nodes;
   unsigned long long rank = ev_prefix[c];
-  if (rank >= hi) return;
-  if (c + 1 < n_chunks && (ev_prefix[c + 1] <= lo || ev_prefix[c + 1] == rank)) return;  // no event of the items array here
+  if (rank >= hi || rank + cnt <= lo) return;  // no event of the items array here
+  if (cnt <= 4) {  // the events kernel left their places behind
+    const unsigned int pack = ev_pack[c];
+    for (unsigned int e = 0; e < cnt; e++, rank++)
+      if (rank >= lo && rank < hi) elem_pos[rank - lo] = c * kChunk + ((pack >> (8 * e)) & 0xFFu) + 1;
+    return;
+  }
   visit_structurals(mk, c, depth0[c], ~0ull, [&](unsigned long long pos, int kind, int d) {
     if ((kind == 0 && d == 1 && json[pos] == '[') || (kind == 2 && d == 2)) {
       if (rank >= lo && rank < hi) elem_pos[rank - lo] = pos + 1;

@@ -140,3 +140,103 @@ def test_300k_node_document(clf, golden):
     batch, got = _device_classify(clf, doc, n)
     assert batch.n_nodes == n
     assert_same_outputs(got, expected_outputs(truth, tid), "300k json")
+
+
+# ---- the paths of the structural-index walker ---------------------------------------------------------------
+def _node(cap=None, conds=None, between="", before_status="", name="n"):
+    """One element of items, compact, with room for junk between capacity and conditions."""
+    st = []
+    if cap is not None:
+        st.append('"capacity":{' + ",".join(json.dumps(k) + ":" + json.dumps(v) for k, v in cap) + "}")
+    if between:
+        st.append(between)
+    if conds is not None:
+        st.append('"conditions":[' + ",".join('{"lastHeartbeatTime":"2025-01-01T00:00:00Z","status":%s,"type":%s,"reason":"r"}'
+                                              % (json.dumps(s), json.dumps(t)) for t, s in conds) + "]")
+    return '{"metadata":{"name":%s}%s,"status":{%s}}' % (json.dumps(name), before_status, ",".join(st))
+
+
+def _doc(nodes):
+    return ('{"kind":"NodeList","items":[' + ",".join(nodes) + "]}").encode()
+
+
+def _check_rows(clf, doc, n, want_general=None):
+    json.loads(doc)
+    batch, got = _device_classify(clf, doc, n)
+    nodes, p, ora = _oracle_classify(doc)
+    assert batch.n_nodes == len(nodes) == n
+    assert_same_outputs(got, ora, "walker paths")
+    assert batch.rows_bytes == p.n_bytes
+    assert batch.rows.cpu().numpy()[:p.n_bytes].tobytes() == p.rows[:p.n_bytes].tobytes()
+    np.testing.assert_array_equal(batch.row_ptr.cpu().numpy().view(np.uint32)[:n + 1], p.row_ptr[:n + 1])
+    t = torch.frombuffer(bytearray(doc), dtype=torch.uint8).cuda()
+    _, info = clf.json_to_pnl(t, n)
+    if want_general is not None:
+        assert int(info[5]) == want_general, f"general-parser nodes {int(info[5])}, expected {want_general}"
+    return int(info[5])
+
+
+READY = [("MemoryPressure", "False"), ("Ready", "True")]
+
+
+def test_plain_documents_take_the_index_walker(clf):
+    """Ordinary API output never touches the byte-serial parser; escapes, duplicates and non-string
+    quantities in the parts that matter send exactly those nodes to it."""
+    tmpl, tid = synth.fleet("g1", 5, 0, 3000)
+    doc = synth.nodelist_json(tmpl, tid, style_fn=lambda i: i % 2)          # plain and whitespace-decorated
+    t = torch.frombuffer(bytearray(doc), dtype=torch.uint8).cuda()
+    _, info = clf.json_to_pnl(t, 3000)
+    assert int(info[5]) == 0
+    nodes = [_node([("nvidia.com/gpu", "4")], READY) for _ in range(40)]
+    nodes[3] = _node([("nvidia.com/gpu", 4)], READY)                         # a number where a string is read
+    nodes[7] = nodes[7].replace('"capacity"', '"c\\u0061pacity"')            # an escaped spelling of a key that matters
+    nodes[11] = nodes[11].replace('"status":{', '"status":{"capacity":{"amd.com/gpu":"1"},')   # duplicate key: last wins
+    nodes[13] = _node([("nvidia.com/gpu", "\\u0038")], READY).replace("\\\\u", "\\u")         # an escape in a quantity
+    nodes[17] = _node([("nvidia.com/gpu", "2")], [("Ready", None)])          # null where a string is read
+    nodes[19] = nodes[19].replace('"type":"Ready"', '"type":"Ready","type":"Gone"')            # duplicate inside a condition
+    _check_rows(clf, _doc(nodes), 40, want_general=6)
+
+
+def test_rows_too_big_for_notes(clf):
+    """More than 16 entries (no notes: the writing pass walks the index again), entries of 255 bytes and more
+    (extended rows), and both mixed with ordinary nodes in one warp."""
+    many = [(f"example.com/res-{i}", str(i)) for i in range(40)] + [("nvidia.com/gpu", "8")]
+    conds20 = [(f"Cond{i}", "False") for i in range(20)] + [("Ready", "True")]
+    longv = [("nvidia.com/gpu", "0" * 300 + "7"), ("k" * 400, "1")]
+    wide = [(f"x{i}", "1") for i in range(300)] + [("amd.com/gpu", "2")]
+    nodes = []
+    for i in range(200):
+        kind = i % 5
+        nodes.append(_node(many, READY) if kind == 0 else _node([("amd.com/gpu", "1")], conds20) if kind == 1
+                     else _node(longv, READY) if kind == 2 else _node(wide, READY) if kind == 3
+                     else _node([("nvidia.com/gpu", "4")], READY))
+    _check_rows(clf, _doc(nodes), 200, want_general=0)
+
+
+def test_texts_far_apart_and_big_blocks(clf):
+    """Capacity and conditions more than a gather span apart (fetched by the owning thread), conditions
+    before capacity (notes refused: capacity is written first), and 128 nodes whose rows exceed the CTA's
+    staging buffer (written straight to global memory)."""
+    junk = '"images":[' + ",".join('{"names":["registry.example/%d"],"sizeBytes":%d}' % (i, i) for i in range(60)) + "]"
+    far = [_node([("nvidia.com/gpu", "2")], READY, between=junk) for _ in range(70)]
+    _check_rows(clf, _doc(far), 70, want_general=0)
+    rev = []
+    for i in range(70):
+        s = _node([("intel.com/gpu", "1"), ("cpu", "8")], READY)
+        a, b = s.index('"capacity"'), s.index(',"conditions"')
+        cap, rest = s[a:b], s[b + 1:-2]
+        rev.append(s[:a] + rest + "," + cap + "}}")
+    _check_rows(clf, _doc(rev), 70, want_general=0)
+    fat = [(f"vendor.example/resource-with-a-long-name-{i:02d}", "1" * 40) for i in range(15)] + [("nvidia.com/gpu", "1")]
+    _check_rows(clf, _doc([_node(fat, READY) for _ in range(300)]), 300, want_general=0)
+    fat2 = [(f"vendor.example/r{i:02d}", "7" * 200) for i in range(12)] + [("nvidia.com/gpu", "1")]      # notes kept, rows of ~3 KB
+    _check_rows(clf, _doc([_node(fat2, READY) for _ in range(200)]), 200, want_general=0)
+
+
+def test_elements_that_are_not_objects_and_odd_values(clf):
+    nodes = ['1', '"s"', '[{"status":{"capacity":{"nvidia.com/gpu":"1"}}}]', 'null', '{}', '{"status":7}', '{"status":"x"}',
+             '{"status":[]}', '{"status":{"capacity":[],"conditions":{}}}', '{"status":{"capacity":{},"conditions":[1,"a",[2],{}]}}',
+             _node([("nvidia.com/gpu", "3")], [("Ready", "True")]),
+             '{"status":{"conditions":[{"type":"Ready","status":"True","extra":{"a":[1,2,{"b":"}"}]}}],"capacity":{"amd.com/gpu":"2"}}}',
+             '{"spec":{"taints":[{"key":"k","value":null}]},"status":{"capacity":{"":"5","nvidia.com/gpu":""},"conditions":[{"type":"","status":""}]}}']
+    _check_rows(clf, _doc(nodes), len(nodes))
