@@ -85,22 +85,27 @@ __device__ __forceinline__ uint32_t flags_to_nibble(uint32_t z) { return (z * 0x
 struct RawMasks {
   uint32_t q, b, o, c, k;
 };
-template <bool ALL>
-__device__ __forceinline__ RawMasks raw_masks(const uint4 lo, const uint4 hi) {
+// quotes and backslashes of one 32-byte group (all the lexer needs)
+__device__ __forceinline__ void raw_quotes(const uint4 lo, const uint4 hi, RawMasks& m) {
   const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-  RawMasks m = {0, 0, 0, 0, 0};
+  m.q = m.b = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) {
     m.q |= flags_to_nibble(eq_bytes(w[i], 0x22222222u)) << (4 * i);
     m.b |= flags_to_nibble(eq_bytes(w[i], 0x5C5C5C5Cu)) << (4 * i);
-    if (ALL) {
-      const uint32_t folded = w[i] & 0xDFDFDFDFu;  // '{' -> '[', '}' -> ']' (nothing else lands on them)
-      m.o |= flags_to_nibble(eq_bytes(folded, 0x5B5B5B5Bu)) << (4 * i);
-      m.c |= flags_to_nibble(eq_bytes(folded, 0x5D5D5D5Du)) << (4 * i);
-      m.k |= flags_to_nibble(eq_bytes(w[i], 0x2C2C2C2Cu)) << (4 * i);
-    }
   }
-  return m;
+}
+// brackets and commas of one group
+__device__ __forceinline__ void raw_brackets(const uint4 lo, const uint4 hi, RawMasks& m) {
+  const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+  m.o = m.c = m.k = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const uint32_t folded = w[i] & 0xDFDFDFDFu;  // '{' -> '[', '}' -> ']' (nothing else lands on them)
+    m.o |= flags_to_nibble(eq_bytes(folded, 0x5B5B5B5Bu)) << (4 * i);
+    m.c |= flags_to_nibble(eq_bytes(folded, 0x5D5D5D5Du)) << (4 * i);
+    m.k |= flags_to_nibble(eq_bytes(w[i], 0x2C2C2C2Cu)) << (4 * i);
+  }
 }
 
 // Bytes escaped by a backslash, given the backslash mask of a group and whether its first byte is
@@ -135,8 +140,20 @@ __device__ __forceinline__ uint32_t prefix_xor(uint32_t x) {
 __device__ __forceinline__ void stage_tile(const uint8_t* __restrict__ json, unsigned long long n, unsigned long long tile_chunk0,
                                            uint8_t* sh) {
   const unsigned long long base = tile_chunk0 * kChunk;
-  constexpr int kVecs = kTileChunks * kChunk / 16;
-  for (int i = threadIdx.x; i < kVecs; i += blockDim.x) {
+  constexpr int kVecs = kTileChunks * kChunk / 16, kPer = kVecs / kTileChunks;  // 16-byte pieces: per tile, per thread
+  if (base + (unsigned long long)kTileChunks * kChunk <= n) {
+    // a whole tile: every load of the thread is in flight before the first store
+    uint4 v[kPer];
+#pragma unroll
+    for (int r = 0; r < kPer; r++) v[r] = __ldg(reinterpret_cast<const uint4*>(json + base) + threadIdx.x + r * kTileChunks);
+#pragma unroll
+    for (int r = 0; r < kPer; r++) {
+      const int i = threadIdx.x + r * kTileChunks;
+      *reinterpret_cast<uint4*>(sh + (i >> 4) * kRowStride + (i & 15) * 16) = v[r];
+    }
+    return;
+  }
+  for (int i = threadIdx.x; i < kVecs; i += kTileChunks) {
     const unsigned long long at = base + 16ull * i;
     uint4 v = make_uint4(0x20202020u, 0x20202020u, 0x20202020u, 0x20202020u);
     if (at + 16 <= n) {
@@ -150,65 +167,198 @@ __device__ __forceinline__ void stage_tile(const uint8_t* __restrict__ json, uns
   }
 }
 
-// pass 1: each chunk's transition function
-__global__ void __launch_bounds__(kTileChunks) lex_summary_kernel(const uint8_t* __restrict__ json, unsigned long long n,
-                                                                  uint8_t* __restrict__ funcs, unsigned long long n_chunks) {
-  extern __shared__ __align__(16) uint8_t sh[];
-  const unsigned long long chunk0 = (unsigned long long)blockIdx.x * kTileChunks;
-  stage_tile(json, n, chunk0, sh);
-  __syncthreads();
-  const unsigned long long c = chunk0 + threadIdx.x;
-  if (c >= n_chunks) return;
-  const uint4* row = reinterpret_cast<const uint4*>(sh + threadIdx.x * kRowStride);
-  uint32_t pe0 = 0, pe1 = 1, par0 = 0, par1 = 0;  // escape carry and quote parity, for e = 0 and e = 1 at the chunk start
-#pragma unroll 2
-  for (int g = 0; g < kGroupsPerChunk; g++) {
-    const RawMasks m = raw_masks<false>(row[2 * g], row[2 * g + 1]);
-    const bool same = pe0 == pe1;
-    const uint32_t q0 = m.q & ~escaped_bytes(m.b, pe0);
-    par0 ^= __popc(q0) & 1;
-    if (same) {
-      pe1 = pe0;
-      par1 ^= __popc(q0) & 1;
-    } else {
-      const uint32_t q1 = m.q & ~escaped_bytes(m.b, pe1);
-      par1 ^= __popc(q1) & 1;
+// ---- one pass over the document: lexer state and depth by decoupled look-back ---------------------------------
+// Tiles are taken in ticket order, so every earlier tile is already running.  A tile publishes what it
+// adds (its transition function; later its bracket balance) as soon as it knows it, then looks back over
+// the tiles before it -- 128 at a time, 4 per lane -- to the nearest one that has published its full
+// prefix, and publishes its own.  State word: flag << 32 | payload, flag 1 = this tile alone, 2 = all tiles
+// up to and including this one.
+constexpr unsigned long long kFlagAgg = 1ull << 32, kFlagInc = 2ull << 32;
+constexpr int kLookWindow = 128;
+
+__device__ __forceinline__ void ld_volatile_2x_u64x2(const unsigned long long* p, unsigned long long (&w)[4]) {
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(p));
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(p + 2));
+}
+struct ComposeMonoid {  // payload: a transition function; order matters
+  static __device__ __forceinline__ uint32_t identity() { return kIdentity; }
+  static __device__ __forceinline__ uint32_t combine(uint32_t first, uint32_t then) { return compose(first, then); }
+};
+struct AddMonoid {      // payload: a bracket balance (int as uint32)
+  static __device__ __forceinline__ uint32_t identity() { return 0u; }
+  static __device__ __forceinline__ uint32_t combine(uint32_t first, uint32_t then) { return first + then; }
+};
+
+// What tile t adds, visible to the tiles after it at once (one thread).
+__device__ __forceinline__ void tile_publish(unsigned long long* st, int t, uint32_t mine) {
+  *reinterpret_cast<volatile unsigned long long*>(st + t) = kFlagAgg | mine;
+}
+// One full warp, some time after tile_publish (whatever the tile can do in between hides the wait).  Returns
+// the combination of tiles [0, t); st[t] goes from "alone" to "prefix".
+template <class M>
+__device__ uint32_t tile_resolve(unsigned long long* st, int t, uint32_t mine, int lane) {
+  uint32_t acc = M::identity();  // tiles [hi, t)
+  int hi = t;
+  while (hi > 0) {
+    const int w0 = (hi - 1) & ~(kLookWindow - 1);  // the aligned window holding tile hi - 1
+    const int base = w0 + 4 * lane;
+    unsigned long long w[4];
+    bool ok, has_inc;
+    int top;
+    while (true) {  // only flags are looked at while waiting; the payloads are combined once, afterwards
+      w[0] = w[1] = w[2] = w[3] = 0;
+      if (base < hi) ld_volatile_2x_u64x2(st + base, w);  // the state array is padded to a whole window
+      ok = true, has_inc = false;
+#pragma unroll
+      for (int k = 3; k >= 0; --k) {  // nearest tile first
+        if (base + k < hi && !has_inc) {
+          const uint32_t flag = (uint32_t)(w[k] >> 32);
+          ok = ok && flag != 0;
+          has_inc = flag == 2u;
+        }
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, has_inc && ok);
+      top = m ? 31 - __clz(m) : -1;  // the nearest tile that knows its full prefix
+      if (__all_sync(0xFFFFFFFFu, lane < top || ok)) break;
+      __nanosleep(64);
     }
+    uint32_t part = M::identity();
+    {
+      bool stop = false;
+#pragma unroll
+      for (int k = 3; k >= 0; --k) {
+        if (base + k < hi && !stop) {
+          part = M::combine((uint32_t)w[k], part);
+          stop = (uint32_t)(w[k] >> 32) == 2u;
+        }
+      }
+    }
+    if (lane < top) part = M::identity();
+    // ordered combination over the lanes: lower lanes hold earlier tiles
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t other = __shfl_down_sync(0xFFFFFFFFu, part, d);
+      if (lane + d < 32) part = M::combine(part, other);
+    }
+    acc = M::combine(__shfl_sync(0xFFFFFFFFu, part, 0), acc);
+    if (top >= 0) break;
+    hi = w0;
   }
-  // f(e | s << 1) = pe_e | (s ^ par_e) << 1
-  const uint32_t f0 = pe0 | (par0 << 1), f1 = pe1 | (par1 << 1), f2 = pe0 | ((par0 ^ 1u) << 1), f3 = pe1 | ((par1 ^ 1u) << 1);
-  funcs[c] = (uint8_t)(f0 | (f1 << 2) | (f2 << 4) | (f3 << 6));
+  if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(st + t) = kFlagInc | M::combine(acc, mine);
+  return acc;
 }
 
-// pass 2: the six masks of every group, the chunk's bracket balance, and a lower bound of the balance inside it
-__global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __restrict__ json, unsigned long long n,
-                                                            const uint8_t* __restrict__ pf, Masks mk, int* __restrict__ delta,
-                                                            int* __restrict__ min_rel, unsigned long long n_chunks) {
+// The six masks of every group, every chunk's depth at its start and a lower bound of the depth inside it.
+__global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk,
+                                                            int* __restrict__ depth0, int* __restrict__ min_rel,
+                                                            unsigned long long* lex_state, unsigned long long* depth_state,
+                                                            unsigned int* ticket, unsigned long long n_chunks) {
   extern __shared__ __align__(16) uint8_t sh[];
-  const unsigned long long chunk0 = (unsigned long long)blockIdx.x * kTileChunks;
+  __shared__ uint32_t s_tile, s_warp[kTileChunks / 32], s_prefix;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const int tile = (int)s_tile;
+  const unsigned long long chunk0 = (unsigned long long)tile * kTileChunks;
   stage_tile(json, n, chunk0, sh);
   __syncthreads();
   const unsigned long long c = chunk0 + threadIdx.x;
-  if (c >= n_chunks) return;
+  const bool have = c < n_chunks;
   const uint4* row = reinterpret_cast<const uint4*>(sh + threadIdx.x * kRowStride);
-  const uint32_t st = pf[c] & 3u;  // (composition of all earlier chunks)(state 0)
-  uint32_t pe = st & 1u, in_str = (st >> 1) ? 0xFFFFFFFFu : 0u;
-  uint4* out = mk.w + c * (2 * kGroupsPerChunk);
-  int bal = 0, low = 0;
+  RawMasks m[kGroupsPerChunk];
+  uint32_t func = kIdentity;
+  if (have) {
+    uint32_t pe0 = 0, pe1 = 1, par0 = 0, par1 = 0;  // escape carry and quote parity, for e = 0 and e = 1 at the chunk start
 #pragma unroll
-  for (int g = 0; g < kGroupsPerChunk; g++) {
-    const RawMasks m = raw_masks<true>(row[2 * g], row[2 * g + 1]);
-    const uint32_t q = m.q & ~escaped_bytes(m.b, pe);
-    const uint32_t s = prefix_xor(q) ^ in_str;  // bit i: byte i is inside a string (opening quote included, closing quote not)
-    in_str = (s >> 31) ? 0xFFFFFFFFu : 0u;
-    const uint32_t o = m.o & ~s, cl = m.c & ~s;
-    out[2 * g] = make_uint4(q & s, q & ~s, o, cl);
-    out[2 * g + 1] = make_uint4(m.k & ~s, m.b & s, 0u, 0u);
-    low = min(low, bal - __popc(cl));  // as if every close of the group came first
-    bal += __popc(o) - __popc(cl);
+    for (int g = 0; g < kGroupsPerChunk; g++) {
+      raw_quotes(row[2 * g], row[2 * g + 1], m[g]);
+      const bool same = pe0 == pe1;
+      const uint32_t q0 = m[g].q & ~escaped_bytes(m[g].b, pe0);
+      par0 ^= __popc(q0) & 1;
+      if (same) {
+        pe1 = pe0;
+        par1 ^= __popc(q0) & 1;
+      } else {
+        const uint32_t q1 = m[g].q & ~escaped_bytes(m[g].b, pe1);
+        par1 ^= __popc(q1) & 1;
+      }
+    }
+    // f(e | s << 1) = pe_e | (s ^ par_e) << 1
+    const uint32_t f0 = pe0 | (par0 << 1), f1 = pe1 | (par1 << 1), f2 = pe0 | ((par0 ^ 1u) << 1), f3 = pe1 | ((par1 ^ 1u) << 1);
+    func = f0 | (f1 << 2) | (f2 << 4) | (f3 << 6);
   }
-  delta[c] = bal;
-  min_rel[c] = low;
+  // ---- lexer state at the start of my chunk: ordered scan inside the CTA, look-back across tiles ----
+  uint32_t inc = func;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t before = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+    if (lane >= d) inc = compose(before, inc);
+  }
+  uint32_t excl = __shfl_up_sync(0xFFFFFFFFu, inc, 1);
+  if (lane == 0) excl = kIdentity;
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  uint32_t tile_func = kIdentity;
+#pragma unroll
+  for (int q = 0; q < kTileChunks / 32; q++) {
+    if (q == warp) excl = compose(tile_func, excl);  // the warps before mine, then the lanes before me
+    tile_func = compose(tile_func, s_warp[q]);
+  }
+  if (threadIdx.x == 0) tile_publish(lex_state, tile, tile_func);
+  // the brackets and commas do not depend on the lexer state: found while the tiles before this one catch up
+  if (have) {
+#pragma unroll
+    for (int g = 0; g < kGroupsPerChunk; g++) raw_brackets(row[2 * g], row[2 * g + 1], m[g]);
+  }
+  if (warp == 0) {
+    const uint32_t before = tile_resolve<ComposeMonoid>(lex_state, tile, tile_func, lane);
+    if (lane == 0) s_prefix = before;
+  }
+  __syncthreads();
+  const uint32_t st = compose(s_prefix, excl) & 3u;  // (every earlier chunk, in order)(state 0)
+  // ---- the masks ----
+  uint32_t pe = st & 1u, in_str = (st >> 1) ? 0xFFFFFFFFu : 0u;
+  int bal = 0, low = 0;
+  if (have) {
+    uint4* out = mk.w + c * (2 * kGroupsPerChunk);
+#pragma unroll
+    for (int g = 0; g < kGroupsPerChunk; g++) {
+      const uint32_t q = m[g].q & ~escaped_bytes(m[g].b, pe);
+      const uint32_t s = prefix_xor(q) ^ in_str;  // bit i: byte i is inside a string (opening quote included, closing quote not)
+      in_str = (s >> 31) ? 0xFFFFFFFFu : 0u;
+      const uint32_t o = m[g].o & ~s, cl = m[g].c & ~s;
+      out[2 * g] = make_uint4(q & s, q & ~s, o, cl);
+      out[2 * g + 1] = make_uint4(m[g].k & ~s, m[g].b & s, 0u, 0u);
+      low = min(low, bal - __popc(cl));  // as if every close of the group came first
+      bal += __popc(o) - __popc(cl);
+    }
+  }
+  // ---- depth at the start of my chunk: sum scan inside the CTA, look-back across tiles ----
+  int dinc = bal;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int before = __shfl_up_sync(0xFFFFFFFFu, dinc, d);
+    if (lane >= d) dinc += before;
+  }
+  __syncthreads();  // s_warp and s_prefix are free again
+  if (lane == 31) s_warp[warp] = (uint32_t)dinc;
+  __syncthreads();
+  int dexcl = dinc - bal, tile_bal = 0;
+#pragma unroll
+  for (int q = 0; q < kTileChunks / 32; q++) {
+    if (q == warp) dexcl += tile_bal;
+    tile_bal += (int)s_warp[q];
+  }
+  if (warp == 0) {
+    if (lane == 0) tile_publish(depth_state, tile, (uint32_t)tile_bal);
+    const uint32_t before = tile_resolve<AddMonoid>(depth_state, tile, (uint32_t)tile_bal, lane);
+    if (lane == 0) s_prefix = before;
+  }
+  __syncthreads();
+  if (have) {
+    depth0[c] = (int)s_prefix + dexcl;
+    min_rel[c] = low;
+  }
 }
 
 // ---- generic exclusive scan over n items, 1024 per block: block totals, scan of totals, apply ---------
