@@ -161,7 +161,9 @@ int gnc_classify_static(int device, const gnc_batch* in, const gnc_result* out, 
  * true/false/null/containers never survive int(str(.)).  Asynchronous on `cuda_stream`.
  * info[0] nodes, info[1] rows_bytes (= row_ptr[nodes]), info[2] status bits (1 no root "items" array,
  * 2 nodes_cap too small, 4 rows_cap too small, 8 unbalanced JSON, 16 too many root-level arrays),
- * info[3]/[4] byte positions of the items array's brackets. */
+ * info[3]/[4] byte positions of the items array's brackets, info[5] how many nodes needed the general
+ * byte-serial parser (escapes, duplicate keys or non-string values in the parts read; 0 on ordinary API
+ * output, which is handled from a bit-mask index of the document).  `json` must be 16-byte aligned. */
 typedef struct gnc_json_out {
   uint8_t* rows;      /* [rows_cap], 16-byte aligned */
   uint32_t* row_ptr;  /* [nodes_cap + 5], 16-byte aligned */
