@@ -515,56 +515,6 @@ __device__ unsigned long long events_before(const uint8_t* json, const Masks& mk
   return cnt;
 }
 
-// One thread: which root-level array is the value of the LAST key "items", and which events are its elements.
-__global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const int* __restrict__ depth0,
-                                  const unsigned int* __restrict__ ev_prefix, Work* w, unsigned int nodes_cap) {
-  if (w->n_open > kMaxRootArrays || w->n_close > kMaxRootArrays) {
-    w->status |= ST_TOO_MANY_ROOT_ARRAYS;
-    w->n_nodes = 0;
-    return;
-  }
-  long long best = -1;
-  for (unsigned int k = 0; k < w->n_open; k++) {
-    const unsigned long long pos = w->root_open[k];
-    long long i = (long long)pos - 1;
-    auto ws = [&](long long j) { return j >= 0 && (json[j] == ' ' || json[j] == '\t' || json[j] == '\n' || json[j] == '\r'); };
-    while (ws(i)) i--;
-    if (i < 0 || json[i] != ':') continue;
-    i--;
-    while (ws(i)) i--;
-    if (i < 6 || json[i] != '"' || json[i - 1] != 's' || json[i - 2] != 'm' || json[i - 3] != 'e' || json[i - 4] != 't' ||
-        json[i - 5] != 'i' || json[i - 6] != '"')
-      continue;
-    if ((long long)pos > best) best = (long long)pos;
-  }
-  if (best < 0) {
-    w->status |= ST_NO_ITEMS;
-    w->n_nodes = 0;
-    return;
-  }
-  unsigned long long end = ~0ull;
-  for (unsigned int k = 0; k < w->n_close; k++)
-    if (w->root_close[k] > (unsigned long long)best && w->root_close[k] < end) end = w->root_close[k];
-  if (end == ~0ull) {
-    w->status |= ST_BAD_JSON;
-    w->n_nodes = 0;
-    return;
-  }
-  w->items_begin = (unsigned long long)best;
-  w->items_end = end;
-  w->ev_base = events_before(json, mk, depth0, ev_prefix, (unsigned long long)best);
-  unsigned long long cnt = events_before(json, mk, depth0, ev_prefix, end) - w->ev_base;   // '[' + commas
-  // an empty array has the '[' event but no element
-  unsigned long long j = (unsigned long long)best + 1;
-  while (j < end && (json[j] == ' ' || json[j] == '\t' || json[j] == '\n' || json[j] == '\r')) j++;
-  if (j == end) cnt = 0;
-  if (cnt > nodes_cap) {
-    w->status |= ST_NODES_CAP;
-    cnt = nodes_cap;
-  }
-  w->n_nodes = (unsigned int)cnt;
-}
-
 // position of the byte after each element's separator
 __global__ void element_starts_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
                                       const unsigned int* __restrict__ ev_count, const unsigned int* __restrict__ ev_pack,
@@ -963,6 +913,65 @@ __device__ void node_locate(const uint8_t* json, unsigned long long n, unsigned 
 __device__ void node_emit(const uint8_t* json, unsigned long long n, const NodePlan& pl, RowOut& o) {
   if (pl.cap_pos != ~0ull) emit_capacity(Cur{json, pl.cap_pos, n}, o);
   if (pl.cond_pos != ~0ull) emit_conditions(Cur{json, pl.cond_pos, n}, o);
+}
+
+// One thread: which root-level array is the value of the LAST key "items", and which events are its elements.
+__global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const int* __restrict__ depth0,
+                                  const unsigned int* __restrict__ ev_prefix, Work* w, unsigned int nodes_cap) {
+  if (w->n_open > kMaxRootArrays || w->n_close > kMaxRootArrays) {
+    w->status |= ST_TOO_MANY_ROOT_ARRAYS;
+    w->n_nodes = 0;
+    return;
+  }
+  long long best = -1;
+  for (unsigned int k = 0; k < w->n_open; k++) {
+    const unsigned long long pos = w->root_open[k];
+    long long i = (long long)pos - 1;
+    auto ws = [&](long long j) { return j >= 0 && (json[j] == ' ' || json[j] == '\t' || json[j] == '\n' || json[j] == '\r'); };
+    while (ws(i)) i--;
+    if (i < 0 || json[i] != ':') continue;
+    i--;
+    while (ws(i)) i--;
+    if (i < 1 || json[i] != '"') continue;
+    // i is the closing quote of the key; its opening quote is the last string-open bit before it.  The key is
+    // compared decoded, so that an escaped spelling of "items" counts as json.loads counts it.
+    long long open = -1;
+    for (long long g = i >> 5; g >= 0 && open < 0; g--) {
+      uint32_t so = mk.w[2 * g].x;
+      if (g == (i >> 5)) so &= (1u << (unsigned)(i & 31)) - 1u;
+      if (so) open = (g << 5) + (31 - __clz(so));
+    }
+    if (open < 0) continue;
+    Cur key{json, (unsigned long long)open, n};
+    if (!string_equals(key, "items", 5)) continue;
+    if ((long long)pos > best) best = (long long)pos;
+  }
+  if (best < 0) {
+    w->status |= ST_NO_ITEMS;
+    w->n_nodes = 0;
+    return;
+  }
+  unsigned long long end = ~0ull;
+  for (unsigned int k = 0; k < w->n_close; k++)
+    if (w->root_close[k] > (unsigned long long)best && w->root_close[k] < end) end = w->root_close[k];
+  if (end == ~0ull) {
+    w->status |= ST_BAD_JSON;
+    w->n_nodes = 0;
+    return;
+  }
+  w->items_begin = (unsigned long long)best;
+  w->items_end = end;
+  w->ev_base = events_before(json, mk, depth0, ev_prefix, (unsigned long long)best);
+  unsigned long long cnt = events_before(json, mk, depth0, ev_prefix, end) - w->ev_base;   // '[' + commas
+  // an empty array has the '[' event but no element
+  unsigned long long j = (unsigned long long)best + 1;
+  while (j < end && (json[j] == ' ' || json[j] == '\t' || json[j] == '\n' || json[j] == '\r')) j++;
+  if (j == end) cnt = 0;
+  if (cnt > nodes_cap) {
+    w->status |= ST_NODES_CAP;
+    cnt = nodes_cap;
+  }
+  w->n_nodes = (unsigned int)cnt;
 }
 
 // ---- fast walker over the structural index --------------------------------------------------------------
