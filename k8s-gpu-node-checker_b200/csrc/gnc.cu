@@ -1054,11 +1054,11 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   const size_t nbc = (n_chunks + 1023) / 1024 + 1, nbn = (nodes_cap + 1023) / 1024 + 1;
   const size_t mask_bytes = (size_t)n_chunks * kChunk;  // the structural index: one byte per document byte
   const size_t n_tiles = (n_chunks + kTileChunks - 1) / kTileChunks, tiles_pad = align_up(n_tiles + 1, kLookWindow);
-  const size_t look_bytes = 2 * tiles_pad * 8 + 256;  // lexer and depth look-back states, then the tile ticket
+  const size_t look_bytes = tiles_pad * 8 + 256;  // lexer look-back states, then the tile ticket
   const size_t o_work = take(sizeof(Work)), o_depth = take(n_chunks * 4), o_evc = take(n_chunks * 4),
                o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
                o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8),
-               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_evpack = take(n_chunks * 4), o_look = take(look_bytes), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
+               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_evpack = take(n_chunks * 4), o_look = take(look_bytes), o_tilebal = take((n_tiles + 1) * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
   if (off > c->json_scratch_bytes) {
     if (c->json_scratch) {
       CUDA_TRY(c, cudaStreamSynchronize(stream));
@@ -1083,8 +1083,10 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   int* min_rel = (int*)(base + o_minrel);
   unsigned int* evpack = (unsigned int*)(base + o_evpack);
   unsigned long long* look = (unsigned long long*)(base + o_look);
-  unsigned long long *lex_state = look, *depth_state = look + tiles_pad;
-  unsigned int* ticket = (unsigned int*)(look + 2 * tiles_pad);
+  unsigned long long* lex_state = look;
+  unsigned int* ticket = (unsigned int*)(look + tiles_pad);
+  int* tile_bal = (int*)(base + o_tilebal);
+  const Depths dp{depth0, tile_bal};
   uint2* desc = (uint2*)(base + o_desc);
   if (!aligned16(json)) return fail(c, GNC_ERR_ARG, "json must be 16-byte aligned");
   CUDA_TRY(c, cudaMemsetAsync(work, 0, sizeof(Work), stream));
@@ -1095,12 +1097,13 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
     constexpr size_t kTileSmem = (size_t)kTileChunks * kRowStride;
     // one pass: masks, per-chunk start depth (lexer state and depth travel from tile to tile by look-back)
     CUDA_TRY(c, cudaMemsetAsync(look, 0, look_bytes, stream));
-    index_kernel<<<tb, kTileChunks, kTileSmem, stream>>>(json, n, mk, depth0, min_rel, lex_state, depth_state, ticket, n_chunks);
-    events_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, min_rel, evc, evpack, work, n_chunks);
+    index_kernel<<<tb, kTileChunks, kTileSmem, stream>>>(json, n, mk, depth0, tile_bal, min_rel, lex_state, ticket, n_chunks);
+    scan_totals_block<int, OpAddI><<<1, 1024, 0, stream>>>(tile_bal, n_tiles, OpAddI(), 0, nullptr);  // tile balances -> tile start depths
+    events_kernel<<<cb, 256, 0, stream>>>(json, mk, dp, min_rel, evc, evpack, work, n_chunks);
     if ((rc = device_exclusive_scan<unsigned int, OpAddU>(c, evc, n_chunks, evp, btu, nullptr, OpAddU(), 0u, stream))) return rc;
-    pick_items_kernel<<<1, 1, 0, stream>>>(json, n, mk, depth0, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
-    element_starts_kernel<<<cb, 256, 0, stream>>>(json, mk, depth0, evc, evpack, evp, work, elem, n_chunks);
-    c->launches += 4;
+    pick_items_kernel<<<1, 1, 0, stream>>>(json, n, mk, dp, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
+    element_starts_kernel<<<cb, 256, 0, stream>>>(json, mk, dp, evc, evpack, evp, work, elem, n_chunks);
+    c->launches += 5;
   }
   const unsigned nb = (unsigned)std::max<unsigned long long>(1, (nodes_cap + 127) / 128);
   if (nodes_cap) {

@@ -62,6 +62,13 @@ struct Masks {
   uint4* w;
 };
 
+// Depth (brackets open outside strings) at the start of a chunk = depth inside its tile + the tile's start depth.
+struct Depths {
+  const int* local;        // [chunks] relative to the start of the chunk's tile
+  const int* tile_start;   // [tiles]
+  __device__ __forceinline__ int at(unsigned long long c) const { return __ldg(tile_start + c / kTileChunks) + __ldg(local + c); }
+};
+
 // ---- lexer state ---------------------------------------------------------------------------------
 // State = e | s << 1: e = the first byte of the chunk is escaped by a backslash before it, s = the chunk
 // starts inside a string.  A chunk's transition function holds 2 bits per start state.  (Backslashes
@@ -167,12 +174,14 @@ __device__ __forceinline__ void stage_tile(const uint8_t* __restrict__ json, uns
   }
 }
 
-// ---- one pass over the document: lexer state and depth by decoupled look-back ---------------------------------
+// ---- one pass over the document: the lexer state travels from tile to tile by decoupled look-back --------------
 // Tiles are taken in ticket order, so every earlier tile is already running.  A tile publishes what it
-// adds (its transition function; later its bracket balance) as soon as it knows it, then looks back over
-// the tiles before it -- 128 at a time, 4 per lane -- to the nearest one that has published its full
-// prefix, and publishes its own.  State word: flag << 32 | payload, flag 1 = this tile alone, 2 = all tiles
-// up to and including this one.
+// adds (its transition function) as soon as it knows it, then looks back over the tiles before it -- 128
+// at a time, 4 per lane -- to the nearest one that has published its full prefix, and publishes its own.
+// State word: flag << 32 | payload, flag 1 = this tile alone, 2 = all tiles up to and including this one.
+// (The bracket depth was first carried the same way, by a second look-back after the masks: nothing was
+// left to hide that wait behind, and a third of the kernel's samples sat at its barrier.  Depths are now
+// written relative to the tile and a small kernel scans the tiles' balances.)
 constexpr unsigned long long kFlagAgg = 1ull << 32, kFlagInc = 2ull << 32;
 constexpr int kLookWindow = 128;
 
@@ -184,11 +193,6 @@ struct ComposeMonoid {  // payload: a transition function; order matters
   static __device__ __forceinline__ uint32_t identity() { return kIdentity; }
   static __device__ __forceinline__ uint32_t combine(uint32_t first, uint32_t then) { return compose(first, then); }
 };
-struct AddMonoid {      // payload: a bracket balance (int as uint32)
-  static __device__ __forceinline__ uint32_t identity() { return 0u; }
-  static __device__ __forceinline__ uint32_t combine(uint32_t first, uint32_t then) { return first + then; }
-};
-
 // What tile t adds, visible to the tiles after it at once (one thread).
 __device__ __forceinline__ void tile_publish(unsigned long long* st, int t, uint32_t mine) {
   *reinterpret_cast<volatile unsigned long long*>(st + t) = kFlagAgg | mine;
@@ -250,8 +254,8 @@ __device__ uint32_t tile_resolve(unsigned long long* st, int t, uint32_t mine, i
 
 // The six masks of every group, every chunk's depth at its start and a lower bound of the depth inside it.
 __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk,
-                                                            int* __restrict__ depth0, int* __restrict__ min_rel,
-                                                            unsigned long long* lex_state, unsigned long long* depth_state,
+                                                            int* __restrict__ depth_local, int* __restrict__ tile_bal,
+                                                            int* __restrict__ min_rel, unsigned long long* lex_state,
                                                             unsigned int* ticket, unsigned long long n_chunks) {
   extern __shared__ __align__(16) uint8_t sh[];
   __shared__ uint32_t s_tile, s_warp[kTileChunks / 32], s_prefix;
@@ -333,30 +337,26 @@ __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __res
       bal += __popc(o) - __popc(cl);
     }
   }
-  // ---- depth at the start of my chunk: sum scan inside the CTA, look-back across tiles ----
+  // ---- depth at the start of my chunk, relative to the tile; the tiles' balances are scanned by a small kernel
+  //      afterwards (a second look-back here would only add a wait at the end of every tile) ----
   int dinc = bal;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const int before = __shfl_up_sync(0xFFFFFFFFu, dinc, d);
     if (lane >= d) dinc += before;
   }
-  __syncthreads();  // s_warp and s_prefix are free again
+  __syncthreads();  // s_warp is free again
   if (lane == 31) s_warp[warp] = (uint32_t)dinc;
   __syncthreads();
-  int dexcl = dinc - bal, tile_bal = 0;
+  int dexcl = dinc - bal, tile_total = 0;
 #pragma unroll
   for (int q = 0; q < kTileChunks / 32; q++) {
-    if (q == warp) dexcl += tile_bal;
-    tile_bal += (int)s_warp[q];
+    if (q == warp) dexcl += tile_total;
+    tile_total += (int)s_warp[q];
   }
-  if (warp == 0) {
-    if (lane == 0) tile_publish(depth_state, tile, (uint32_t)tile_bal);
-    const uint32_t before = tile_resolve<AddMonoid>(depth_state, tile, (uint32_t)tile_bal, lane);
-    if (lane == 0) s_prefix = before;
-  }
-  __syncthreads();
+  if (threadIdx.x == 0) tile_bal[tile] = tile_total;
   if (have) {
-    depth0[c] = (int)s_prefix + dexcl;
+    depth_local[c] = dexcl;
     min_rel[c] = low;
   }
 }
@@ -469,18 +469,19 @@ __device__ __forceinline__ int visit_structurals(const Masks& mk, unsigned long 
 }
 
 // events: the '[' of every root-level array and every ',' directly inside one (depth 2 outside strings)
-__global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
+__global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths dp,
                               const int* __restrict__ min_rel, unsigned int* __restrict__ ev_count, unsigned int* __restrict__ ev_pack,
                               Work* w, unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
   if (c >= n_chunks) return;
   unsigned int cnt = 0, pack = 0;  // pack: where in the chunk the first four events are (element_starts_kernel reads it)
-  if (depth0[c] + min_rel[c] > 2) {  // the whole chunk lies deeper than the root levels
+  const int d0 = dp.at(c);
+  if (d0 + min_rel[c] > 2) {  // the whole chunk lies deeper than the root levels
     ev_count[c] = 0;
     return;
   }
   const unsigned long long chunk_base = c * kChunk;
-  visit_structurals(mk, c, depth0[c], ~0ull, [&](unsigned long long pos, int kind, int d) {
+  visit_structurals(mk, c, d0, ~0ull, [&](unsigned long long pos, int kind, int d) {
     if (kind == 0 && d == 1) {
       if (json[pos] == '[') {
         if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
@@ -505,18 +506,18 @@ __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, const 
 }
 
 // number of events strictly before byte `pos` (pos lies outside strings)
-__device__ unsigned long long events_before(const uint8_t* json, const Masks& mk, const int* depth0, const unsigned int* ev_prefix,
+__device__ unsigned long long events_before(const uint8_t* json, const Masks& mk, const Depths& dp, const unsigned int* ev_prefix,
                                             unsigned long long pos) {
   const unsigned long long c = pos / kChunk;
   unsigned long long cnt = ev_prefix[c];
-  visit_structurals(mk, c, depth0[c], pos, [&](unsigned long long at, int kind, int d) {
+  visit_structurals(mk, c, dp.at(c), pos, [&](unsigned long long at, int kind, int d) {
     if ((kind == 0 && d == 1 && json[at] == '[') || (kind == 2 && d == 2)) cnt++;
   });
   return cnt;
 }
 
 // position of the byte after each element's separator
-__global__ void element_starts_kernel(const uint8_t* __restrict__ json, Masks mk, const int* __restrict__ depth0,
+__global__ void element_starts_kernel(const uint8_t* __restrict__ json, Masks mk, Depths dp,
                                       const unsigned int* __restrict__ ev_count, const unsigned int* __restrict__ ev_pack,
                                       const unsigned int* __restrict__ ev_prefix, const Work* w,
                                       unsigned long long* __restrict__ elem_pos, unsigned long long n_chunks) {
@@ -533,7 +534,7 @@ __global__ void element_starts_kernel(const uint8_t* __restrict__ json, Masks mk
       if (rank >= lo && rank < hi) elem_pos[rank - lo] = c * kChunk + ((pack >> (8 * e)) & 0xFFu) + 1;
     return;
   }
-  visit_structurals(mk, c, depth0[c], ~0ull, [&](unsigned long long pos, int kind, int d) {
+  visit_structurals(mk, c, dp.at(c), ~0ull, [&](unsigned long long pos, int kind, int d) {
     if ((kind == 0 && d == 1 && json[pos] == '[') || (kind == 2 && d == 2)) {
       if (rank >= lo && rank < hi) elem_pos[rank - lo] = pos + 1;
       rank++;
@@ -916,7 +917,7 @@ __device__ void node_emit(const uint8_t* json, unsigned long long n, const NodeP
 }
 
 // One thread: which root-level array is the value of the LAST key "items", and which events are its elements.
-__global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const int* __restrict__ depth0,
+__global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk, Depths dp,
                                   const unsigned int* __restrict__ ev_prefix, Work* w, unsigned int nodes_cap) {
   if (w->n_open > kMaxRootArrays || w->n_close > kMaxRootArrays) {
     w->status |= ST_TOO_MANY_ROOT_ARRAYS;
@@ -961,8 +962,8 @@ __global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned lon
   }
   w->items_begin = (unsigned long long)best;
   w->items_end = end;
-  w->ev_base = events_before(json, mk, depth0, ev_prefix, (unsigned long long)best);
-  unsigned long long cnt = events_before(json, mk, depth0, ev_prefix, end) - w->ev_base;   // '[' + commas
+  w->ev_base = events_before(json, mk, dp, ev_prefix, (unsigned long long)best);
+  unsigned long long cnt = events_before(json, mk, dp, ev_prefix, end) - w->ev_base;   // '[' + commas
   // an empty array has the '[' event but no element
   unsigned long long j = (unsigned long long)best + 1;
   while (j < end && (json[j] == ' ' || json[j] == '\t' || json[j] == '\n' || json[j] == '\r')) j++;
