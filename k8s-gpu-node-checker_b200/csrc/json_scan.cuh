@@ -92,27 +92,29 @@ __device__ __forceinline__ uint32_t flags_to_nibble(uint32_t z) { return (z * 0x
 struct RawMasks {
   uint32_t q, b, o, c, k;
 };
-// quotes and backslashes of one 32-byte group (all the lexer needs)
-__device__ __forceinline__ void raw_quotes(const uint4 lo, const uint4 hi, RawMasks& m) {
-  const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-  m.q = m.b = 0;
-#pragma unroll
+// quotes and backslashes of one 32-byte group (all the lexer needs).  The word loops are kept rolled: fully
+// unrolled, the kernel's code no longer fits the instruction cache (15 % of its samples were instruction fetch).
+__device__ __forceinline__ void raw_quotes(const uint32_t* __restrict__ w, RawMasks& m) {
+  uint32_t q = 0, b = 0;
+#pragma unroll 2
   for (int i = 0; i < 8; i++) {
-    m.q |= flags_to_nibble(eq_bytes(w[i], 0x22222222u)) << (4 * i);
-    m.b |= flags_to_nibble(eq_bytes(w[i], 0x5C5C5C5Cu)) << (4 * i);
+    const uint32_t x = w[i];
+    q |= flags_to_nibble(eq_bytes(x, 0x22222222u)) << (4 * i);
+    b |= flags_to_nibble(eq_bytes(x, 0x5C5C5C5Cu)) << (4 * i);
   }
+  m.q = q, m.b = b;
 }
 // brackets and commas of one group
-__device__ __forceinline__ void raw_brackets(const uint4 lo, const uint4 hi, RawMasks& m) {
-  const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-  m.o = m.c = m.k = 0;
-#pragma unroll
+__device__ __forceinline__ void raw_brackets(const uint32_t* __restrict__ w, RawMasks& m) {
+  uint32_t o = 0, c = 0, k = 0;
+#pragma unroll 2
   for (int i = 0; i < 8; i++) {
-    const uint32_t folded = w[i] & 0xDFDFDFDFu;  // '{' -> '[', '}' -> ']' (nothing else lands on them)
-    m.o |= flags_to_nibble(eq_bytes(folded, 0x5B5B5B5Bu)) << (4 * i);
-    m.c |= flags_to_nibble(eq_bytes(folded, 0x5D5D5D5Du)) << (4 * i);
-    m.k |= flags_to_nibble(eq_bytes(w[i], 0x2C2C2C2Cu)) << (4 * i);
+    const uint32_t x = w[i], folded = x & 0xDFDFDFDFu;  // '{' -> '[', '}' -> ']' (nothing else lands on them)
+    o |= flags_to_nibble(eq_bytes(folded, 0x5B5B5B5Bu)) << (4 * i);
+    c |= flags_to_nibble(eq_bytes(folded, 0x5D5D5D5Du)) << (4 * i);
+    k |= flags_to_nibble(eq_bytes(x, 0x2C2C2C2Cu)) << (4 * i);
   }
+  m.o = o, m.c = c, m.k = k;
 }
 
 // Bytes escaped by a backslash, given the backslash mask of a group and whether its first byte is
@@ -275,7 +277,7 @@ __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __res
     uint32_t pe0 = 0, pe1 = 1, par0 = 0, par1 = 0;  // escape carry and quote parity, for e = 0 and e = 1 at the chunk start
 #pragma unroll
     for (int g = 0; g < kGroupsPerChunk; g++) {
-      raw_quotes(row[2 * g], row[2 * g + 1], m[g]);
+      raw_quotes(reinterpret_cast<const uint32_t*>(row + 2 * g), m[g]);
       const bool same = pe0 == pe1;
       const uint32_t q0 = m[g].q & ~escaped_bytes(m[g].b, pe0);
       par0 ^= __popc(q0) & 1;
@@ -312,7 +314,7 @@ __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __res
   // the brackets and commas do not depend on the lexer state: found while the tiles before this one catch up
   if (have) {
 #pragma unroll
-    for (int g = 0; g < kGroupsPerChunk; g++) raw_brackets(row[2 * g], row[2 * g + 1], m[g]);
+    for (int g = 0; g < kGroupsPerChunk; g++) raw_brackets(reinterpret_cast<const uint32_t*>(row + 2 * g), m[g]);
   }
   if (warp == 0) {
     const uint32_t before = tile_resolve<ComposeMonoid>(lex_state, tile, tile_func, lane);
