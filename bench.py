@@ -245,14 +245,16 @@ def run_b200(args):
     barrier()
     total_ms = t_start.elapsed_time(t_end)
     kern_ms = [a.elapsed_time(b) for a, b in k_ev]
+    # what follows each classify launch on the stream until the next one starts: the gather (N > 1) and launch gaps
+    tail_ms = [k_ev[i][1].elapsed_time(k_ev[i + 1][0]) for i in range(args.steps - 1)] or [0.0]
     launches = clf.launches - launches0
     clocks = sampler.stop() if sampler else None
     if world > 1:
-        t = torch.tensor([total_ms, statistics.mean(kern_ms)], device=dev, dtype=torch.float64)
+        t = torch.tensor([total_ms, statistics.mean(kern_ms), statistics.mean(tail_ms)], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, kern_mean = float(t[0]), float(t[1])
+        total_ms, kern_mean, tail_mean = float(t[0]), float(t[1]), float(t[2])
     else:
-        kern_mean = statistics.mean(kern_ms)
+        kern_mean, tail_mean = statistics.mean(kern_ms), statistics.mean(tail_ms)
 
     counts = (fleet.counts if world > 1 else out.counts).cpu().numpy()
     g_fleet = int(counts[0])
@@ -317,7 +319,7 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": NCU_TRAFFIC_BYTES_DEFAULT_WORKLOAD if (world == 1 and n_total == FLEET_NODES) else None,
                      "traffic_source": "profiles/r01_ncu_classify_10m.txt (ncu --set full, one launch)", "peak_source": peak_src, "kernel": "gnc::classify_kernel",
-                     "kernel_ms": kern_mean, "algorithmic_bytes_per_launch": int(algo_bytes),
+                     "kernel_ms": kern_mean, "after_kernel_ms": tail_mean, "algorithmic_bytes_per_launch": int(algo_bytes),
                      "bytes_per_node": algo_bytes / n, "frac_of_8TBps": achieved / 8000.0},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }

@@ -7,24 +7,25 @@
 // (duplicate object keys: last wins; \uXXXX escapes, surrogate pairs joined, lone surrogates kept).
 //
 // Structure: a structural index first (bit masks, one bit per byte), then everything walks the masks.
-//   1. summary: 256-byte chunks staged through shared memory; per 32-byte group the quote and backslash
-//               bit masks (SWAR byte compares); each chunk's effect on the lexer state {escape pending,
-//               inside string} as a function table; an exclusive scan of function COMPOSITIONS gives
-//               every chunk its start state
-//   2. index:   with the start state known: escaped bytes, unescaped quotes, in-string mask (prefix
-//               xor), and from them six masks per group -- string opens, string closes, brackets open /
-//               close outside strings, commas outside strings, backslashes inside strings -- plus the
-//               chunk's bracket balance; a sum scan gives every chunk its start depth
-//   3. events:  element separators of root-level arrays (the '[' itself and each ',' at depth 2) are
+//   1. index:   one pass over the document (index_kernel).  32 KB tiles staged through shared memory, a
+//               256-byte chunk per thread; per 32-byte group the quote and backslash masks by SWAR byte
+//               compares; each chunk's effect on the lexer state {escape pending, inside string} as a
+//               transition function, scanned inside the CTA and carried from tile to tile by decoupled
+//               look-back.  With the start state known: escaped bytes, unescaped quotes, in-string mask
+//               (prefix xor), and six masks per group -- string opens, string closes, brackets open /
+//               close outside strings, commas outside strings, backslashes inside strings -- plus every
+//               chunk's start depth relative to its tile; a small kernel scans the tiles' bracket balances
+//   2. events:  element separators of root-level arrays (the '[' itself and each ',' at depth 2) are
 //               counted per chunk from the masks and scanned; root-level array brackets are listed; one
 //               thread then picks the LAST root key "items" and the range of events that are its elements
-//   4. nodes:   one thread per element.  The fast walker steps from structural bit to structural bit
-//               (find-first-set over the masks; containers that do not matter are skipped a group at a
-//               time by popcount) and touches document bytes only to compare the few keys that matter
-//               and to copy capacity / condition text.  Anything unusual in the parts that matter -- an
-//               escape in a key or value, a duplicate of a key that matters, a non-string quantity -- sends
-//               that node to the general byte-serial parser below, which implements the full semantics.
-//               Two passes (measure, scan of row sizes, write).
+//   3. nodes:   one thread per element, whole warps in step.  The fast walker steps from structural bit
+//               to structural bit (find-first-set over the masks; containers that do not matter are
+//               skipped a group at a time by popcount) and touches document bytes only to compare the few
+//               keys that matter.  Anything unusual in the parts that matter -- an escape in a key or
+//               value, a duplicate of a key that matters, a non-string quantity -- sends that node to the
+//               general byte-serial parser below, which implements the full semantics.  Two passes:
+//               measure (notes where every row entry's text is), scan of row sizes, write (warps gather
+//               the noted texts together, rows are assembled in shared memory and copied out coalesced).
 #pragma once
 
 #include <cuda_runtime.h>
