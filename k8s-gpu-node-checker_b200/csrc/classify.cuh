@@ -644,6 +644,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
     }
     mbar_init_fence();
   }
+  if (tid == 0) GNC_T(7, 0, gtimer());  // CTA entry
   if (tid < GNC_N_COUNTS) sm.acc[tid] = 0;
   if (tid < kRing) sm.tile_cnt[tid] = 0;
   if (FLEET && tid < (int)p.fleet_world && p.fleet_ack_need) {
@@ -925,6 +926,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       lag_first[0] = first;
       if (tid == 0) GNC_T(4, it, gtimer());
     }
+    if (tid == 0) GNC_T(7, 1, gtimer());  // last tile walked
     // drain the ring, then release both scan warps: their next phase completes with no tile
 #pragma unroll
     for (int q = kRing - 2; q >= 0; q--)
@@ -938,34 +940,44 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
 
   // ------------------------------ grid-wide finish ------------------------------
   __syncthreads();
-  if (tid == 0) {
-    ScratchHeader* sc = p.scratch;
-#pragma unroll
-    for (int c = 0; c < GNC_N_COUNTS; c++) {
-      if (c >= GNC_C_KEY_LO && c < GNC_C_KEY_HI) {  // lo with carry into hi
-        unsigned long long v = sm.acc[c];
-        if (v) {
-          unsigned long long old = atomicAdd(&sc->accum[c], v);
-          if (old + v < old) atomicAdd(&sc->accum[c + 4], 1ull);
-        }
-      } else if (sm.acc[c]) {
-        atomicAdd(&sc->accum[c], sm.acc[c]);
+  if (tid == 0) GNC_T(7, 2, gtimer());  // ring drained, every warp here
+  // One thread per count: done by thread 0 alone, the sixteen dependent round trips to L2 here and in the
+  // last CTA below were ~10 us at the very end of every launch.
+  ScratchHeader* sc = p.scratch;
+  if (tid < GNC_N_COUNTS) {
+    const int c = tid;
+    const unsigned long long v = sm.acc[c];
+    if (c >= GNC_C_KEY_LO && c < GNC_C_KEY_HI) {  // lo with carry into hi
+      if (v) {
+        const unsigned long long old = atomicAdd(&sc->accum[c], v);
+        if (old + v < old) atomicAdd(&sc->accum[c + 4], 1ull);
       }
+    } else if (v) {
+      atomicAdd(&sc->accum[c], v);
     }
+  }
+  __syncthreads();
+  if (tid == 0) {
     if (FLEET) __threadfence_system();  // this CTA's peer stores are out before it counts as done
     else __threadfence();
     const uint32_t prev = atomicAdd(&sc->done, 1u);
-    if (prev == gridDim.x - 1) {  // last CTA: publish the counts block and re-arm the scratch
-      __threadfence();
-      for (int c = 0; c < GNC_N_COUNTS; c++) {
-        long long v = (long long)ld_volatile_u64(&sc->accum[c]);
-        if (c == GNC_C_SCANNED) v = p.n_nodes;
-        p.counts[c] = v;
-        sc->accum[c] = 0;
-        if (FLEET)
-          for (uint32_t q = 0; q < p.fleet_world; q++)
-            reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[c] = v;
-      }
+    __threadfence();
+    sm.tile_cnt[0] = prev == gridDim.x - 1 ? 1u : 0u;  // (the ring's counters are idle by now)
+  }
+  __syncthreads();
+  if (sm.tile_cnt[0]) {  // last CTA: publish the counts block and re-arm the scratch
+    if (tid < GNC_N_COUNTS) {
+      const int c = tid;
+      long long v = (long long)ld_volatile_u64(&sc->accum[c]);
+      if (c == GNC_C_SCANNED) v = p.n_nodes;
+      p.counts[c] = v;
+      sc->accum[c] = 0;
+      if (FLEET)
+        for (uint32_t q = 0; q < p.fleet_world; q++)
+          reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[c] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {
       if (FLEET) {  // every index and the counts are on their way: raise this rank's flag everywhere
         __threadfence_system();
         for (uint32_t q = 0; q < p.fleet_world; q++) st_sys_u64(p.fleet_flag[q] + p.fleet_rank, p.fleet_epoch);
@@ -976,6 +988,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       sc->done = 0;
     }
   }
+  if (tid == 0) GNC_T(7, 3, gtimer());  // CTA exit
 }
 
 }  // namespace gnc
