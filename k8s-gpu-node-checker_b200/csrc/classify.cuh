@@ -57,7 +57,12 @@ constexpr int kLookbackSpan = 16;                   // tiles per lane per round
 constexpr int kLookbackWindow = 32 * kLookbackSpan; // tiles per round
 
 constexpr int kFleetMaxWorld = 8;
-constexpr uint32_t kFleetHeader = 2 * GNC_N_COUNTS;  // a slot starts with the rank's counts block (16 x i64)
+// A rank's slot in a fleet buffer: the counts block (16 x i64), then {tile nodes, tiles, node_base, nodes}, then
+// one record per tile: the tile's exclusive GPU-node prefix within the shard and its walker warps' GPU-node
+// ballots (tile_nodes / 32 words).  Which nodes are GPU nodes travels as bit masks, 1/20 of the bytes of the
+// index list; every rank rebuilds the ordered indices from them locally.
+constexpr uint32_t kFleetHeader = 2 * GNC_N_COUNTS + 8;
+enum : int { FLEET_H_TILE_NODES = 2 * GNC_N_COUNTS, FLEET_H_TILES, FLEET_H_NODE_BASE, FLEET_H_NODES };
 constexpr unsigned long long kFleetTimeoutNs = 2000000000ull;
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -95,11 +100,11 @@ struct Params {
   unsigned long long* inc;  // [tiles rounded up to the look-back window]
   uint32_t* agg;            // likewise
   unsigned long long* trace;  // debug builds only (GNC_TRACE): [cta][iteration][8] timestamps
-  // Fused gather (multi-GPU, gnc_fleet_enable): every GPU node's index is also stored straight into
-  // every rank's fleet buffer over NVLink while the kernel runs, so that no collective follows it.
+  // Fused gather (multi-GPU, gnc_fleet_enable): every tile's GPU-node ballots and prefix are also stored
+  // straight into every rank's fleet buffer over NVLink while the kernel runs, so that no collective follows it.
   uint32_t fleet_world;                      // 0: off
   uint32_t fleet_rank;
-  uint32_t fleet_cap;                        // indices per slot
+  uint32_t fleet_cap;                        // record words per slot
   uint32_t fleet_slot_u32;                   // u32 per slot: kFleetHeader + fleet_cap
   unsigned long long fleet_epoch;            // this launch's number
   unsigned long long fleet_ack_need;         // every peer must have consumed this epoch before its slots are rewritten
@@ -764,6 +769,8 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, kWalkWarps - 1);
       const uint32_t excl = lookback(p, tile, total, lane);
       if (lane < kWalkWarps) sm.warp_base[b][lane] = excl + incl - c;
+      if (FLEET && lane < (int)p.fleet_world && (uint32_t)(tile + 1) * (kWalkWarps + 1) <= p.fleet_cap)  // one lane per peer
+        p.fleet_peer[lane][p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1)] = excl;
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.pref_full[b]);
       GNC_T(6, it, gtimer());
@@ -809,10 +816,6 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
             v0 = (short)(sv.x & 0xFFFFu), v1 = (short)(sv.x >> 16), v2 = (short)(sv.y & 0xFFFFu), v3 = (short)(sv.y >> 16);
           }
           p.gpu_idx[pos] = p.node_base + first_e + j;
-          if (FLEET && pos < p.fleet_cap) {
-            const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + pos;
-            for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][at] = p.node_base + first_e + j;
-          }
           p.gpu_total[pos] = v0 + v1 + v2 + v3;
           longlong2* vo = reinterpret_cast<longlong2*>(p.gpu_vals + 4ull * pos);
           vo[0] = make_longlong2(v0, v1);
@@ -895,6 +898,10 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         pp[0] = make_int4(__popc(gb), (int)n_ready, (int)n_def, (int)n_bad);  // P_GPU, P_READY, P_DEFERRED, P_MALFORMED
         pp[1] = make_int4(s0, s1, s2, s3);                                     // P_KEY0 ..
         if (warp == 0) sm.scan_tile[b] = tile;
+        if (FLEET && (uint32_t)(tile + 1) * (kWalkWarps + 1) <= p.fleet_cap) {
+          const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1) + 1 + warp;
+          for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][at] = gb;
+        }
         // the last warp to count its share publishes the tile's aggregate at once: other CTAs'
         // look-backs must never wait for this CTA's scan warp to get round to the tile
         const uint32_t old = atomicAdd(&sm.tile_cnt[b], (uint32_t)__popc(gb) | (1u << 16));
@@ -975,6 +982,10 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       if (FLEET)
         for (uint32_t q = 0; q < p.fleet_world; q++)
           reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[c] = v;
+    } else if (FLEET && tid < GNC_N_COUNTS + 4) {  // what the receivers need to read the tile records
+      const int h = FLEET_H_TILE_NODES + tid - GNC_N_COUNTS;
+      const uint32_t v = h == FLEET_H_TILE_NODES ? (uint32_t)TN : h == FLEET_H_TILES ? p.num_tiles : h == FLEET_H_NODE_BASE ? p.node_base : p.n_nodes;
+      for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][(size_t)p.fleet_rank * p.fleet_slot_u32 + h] = v;
     }
     __syncthreads();
     if (tid == 0) {

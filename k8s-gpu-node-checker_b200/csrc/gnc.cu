@@ -93,6 +93,7 @@ struct gnc_ctx {
     uint32_t cap = 0, slot_u32 = 0;
     size_t region_bytes = 0, bytes = 0;
     char* base[gnc::kFleetMaxWorld] = {};  // every rank's fleet buffer as mapped here (own: local allocation)
+    uint32_t shard_nodes = 0;              // the largest shard a slot has room for
     unsigned long long epoch = 0;
     unsigned int* unpack_done = nullptr;
   } fleet;
@@ -190,6 +191,10 @@ __global__ void fleet_publish_empty_kernel(const Params p) {
     for (uint32_t q = 0; q < p.fleet_world; q++)
       for (int s = 0; s < GNC_N_COUNTS; s++)
         reinterpret_cast<long long*>(p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32)[s] = 0;
+    for (uint32_t q = 0; q < p.fleet_world; q++) {
+      uint32_t* h = p.fleet_peer[q] + (size_t)p.fleet_rank * p.fleet_slot_u32;
+      h[gnc::FLEET_H_TILE_NODES] = 32, h[gnc::FLEET_H_TILES] = 0, h[gnc::FLEET_H_NODE_BASE] = p.node_base, h[gnc::FLEET_H_NODES] = 0;
+    }
     __threadfence_system();
     for (uint32_t q = 0; q < p.fleet_world; q++) gnc::st_sys_u64(p.fleet_flag[q] + p.fleet_rank, p.fleet_epoch);
   }
@@ -199,12 +204,17 @@ struct AckPtrs {
   unsigned long long* p[gnc::kFleetMaxWorld];
 };
 
-// Wait until every rank's slot of this epoch has arrived in the LOCAL fleet buffer, then build the dense
-// rank-ordered index list and the summed counts, then tell every rank that its slot here was consumed.
-__global__ void fleet_unpack_kernel(const uint32_t* slots, const unsigned long long* flags, unsigned long long epoch, int world, int rank,
-                                    uint32_t slot_u32, uint32_t cap, uint32_t* out_idx, uint32_t out_cap, int64_t* out_counts,
-                                    unsigned int* done, AckPtrs ack_peer) {
-  __shared__ unsigned long long off[gnc::kFleetMaxWorld + 1];
+// Wait until every rank's slot of this epoch has arrived in the LOCAL fleet buffer, then rebuild the dense
+// rank-ordered index list from the tile records (prefix + GPU-node ballots) and sum the counts, then tell
+// every rank that its slot here was consumed.  A warp takes 32 consecutive ballot words of one rank: their
+// indices are one contiguous piece of the output, assembled in shared memory and stored coalesced.
+constexpr int kUnpackWarps = 8;
+__global__ void __launch_bounds__(kUnpackWarps * 32) fleet_unpack_kernel(
+    const uint32_t* slots, const unsigned long long* flags, unsigned long long epoch, int world, int rank, uint32_t slot_u32, uint32_t cap,
+    uint32_t* out_idx, uint32_t out_cap, int64_t* out_counts, unsigned int* done, AckPtrs ack_peer) {
+  __shared__ unsigned long long off[gnc::kFleetMaxWorld + 1];   // GPU nodes before each rank
+  __shared__ unsigned long long goff[gnc::kFleetMaxWorld + 1];  // 32-word groups before each rank
+  __shared__ uint32_t buf[kUnpackWarps][1024];
   __shared__ int timed_out;
   if (threadIdx.x == 0) timed_out = 0;
   __syncthreads();
@@ -219,37 +229,54 @@ __global__ void fleet_unpack_kernel(const uint32_t* slots, const unsigned long l
   __syncthreads();
   __threadfence_system();
   if (threadIdx.x == 0) {
-    off[0] = 0;
-    for (int r = 0; r < world; r++) off[r + 1] = off[r] + (unsigned long long)reinterpret_cast<const long long*>(slots + (size_t)r * slot_u32)[GNC_C_GPU_NODES];
+    off[0] = goff[0] = 0;
+    for (int r = 0; r < world; r++) {
+      const uint32_t* h = slots + (size_t)r * slot_u32;
+      const unsigned long long words = (unsigned long long)__ldcv(h + gnc::FLEET_H_TILES) * (__ldcv(h + gnc::FLEET_H_TILE_NODES) / 32);
+      off[r + 1] = off[r] + (unsigned long long)__ldcv(reinterpret_cast<const long long*>(h) + GNC_C_GPU_NODES);
+      goff[r + 1] = goff[r] + (words + 31) / 32;
+    }
   }
   __syncthreads();
-  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x, t0 = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-  // 16 bytes per load, four loads in flight per thread: one 4-byte load per round trip made this copy
-  // (28 MB at 10M nodes, whatever the world size) the longest part of the gather
-  for (int r = 0; r < world; r++) {
-    const uint32_t* src = slots + (size_t)r * slot_u32 + gnc::kFleetHeader;  // 16-byte aligned: header and cap are multiples of 4 words
-    const unsigned long long cnt = min(off[r + 1] - off[r], (unsigned long long)cap), n4 = cnt >> 2, o0 = off[r];
-    const uint4* src4 = reinterpret_cast<const uint4*>(src);
-    for (unsigned long long i = t0; i < n4; i += 4 * stride) {
-      uint4 v[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) v[u] = i + u * stride < n4 ? __ldcv(src4 + i + u * stride) : make_uint4(0, 0, 0, 0);
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const unsigned long long e = o0 + 4 * (i + u * stride);
-        if (i + u * stride < n4) {
-          if (e + 3 < out_cap) {
-            out_idx[e] = v[u].x, out_idx[e + 1] = v[u].y, out_idx[e + 2] = v[u].z, out_idx[e + 3] = v[u].w;
-          } else {
-            if (e < out_cap) out_idx[e] = v[u].x;
-            if (e + 1 < out_cap) out_idx[e + 1] = v[u].y;
-            if (e + 2 < out_cap) out_idx[e + 2] = v[u].z;
-          }
-        }
-      }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned long long n_warps = (unsigned long long)gridDim.x * kUnpackWarps;
+  for (unsigned long long grp = (unsigned long long)blockIdx.x * kUnpackWarps + warp; grp < goff[world]; grp += n_warps) {
+    int r = 0;
+    while (grp >= goff[r + 1]) r++;
+    const uint32_t* h = slots + (size_t)r * slot_u32;
+    const uint32_t tn = __ldcv(h + gnc::FLEET_H_TILE_NODES), wpt = tn / 32, tiles = __ldcv(h + gnc::FLEET_H_TILES);
+    const uint32_t node_base = __ldcv(h + gnc::FLEET_H_NODE_BASE);
+    const unsigned long long words = (unsigned long long)tiles * wpt, j = (grp - goff[r]) * 32 + lane;
+    const uint32_t tile = (uint32_t)(j / wpt), w = (uint32_t)(j % wpt);
+    const uint32_t* rec = h + gnc::kFleetHeader + (size_t)tile * (wpt + 1);
+    const bool have = j < words && (unsigned long long)(tile + 1) * (wpt + 1) <= cap;
+    const uint32_t m = have ? __ldcv(rec + 1 + w) : 0u;
+    const uint32_t cnt = __popc(m);
+    // where the group starts in the rank's list: the first word's tile prefix + the GPU nodes of the tile's earlier warps
+    uint32_t start = 0;
+    if (lane == 0 && have) {
+      start = __ldcv(rec);
+      for (uint32_t u = 0; u < w; u++) start += __popc(__ldcv(rec + 1 + u));
     }
-    const unsigned long long tail = (n4 << 2) + t0;  // the last cnt % 4 indices
-    if (tail < cnt && o0 + tail < out_cap) out_idx[o0 + tail] = __ldcv(src + tail);
+    start = __shfl_sync(0xFFFFFFFFu, start, 0);
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    uint32_t at = incl - cnt, mm = m;
+    const uint32_t node0 = node_base + tile * tn + 32 * w;
+    while (mm) {
+      buf[warp][at++] = node0 + (__ffs(mm) - 1);
+      mm &= mm - 1;
+    }
+    __syncwarp();
+    const unsigned long long o0 = off[r] + start;
+    for (uint32_t k = lane; k < total; k += 32)
+      if (o0 + k < out_cap) out_idx[o0 + k] = buf[warp][k];
+    __syncwarp();
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     long long sum[GNC_N_COUNTS];
@@ -261,8 +288,6 @@ __global__ void fleet_unpack_kernel(const uint32_t* slots, const unsigned long l
       for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] += cr[s];
       for (int k = 0; k < 4; k++)
         key[k] += ((unsigned __int128)(unsigned long long)cr[GNC_C_KEY_HI + k] << 64) | (unsigned long long)cr[GNC_C_KEY_LO + k];
-      const unsigned long long cnt = off[r + 1] - off[r];
-      if (cnt > cap) lost += cnt - cap;
     }
     if (off[world] > out_cap) lost = max(lost, off[world] - out_cap);
     for (int k = 0; k < 4; k++) {
@@ -391,7 +416,10 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
 #ifdef GNC_TRACE
   p.trace = c->trace;
 #endif
-  if (c->fleet.on) fleet_params(c, &p);
+  if (c->fleet.on) {
+    if (in->n_nodes > c->fleet.shard_nodes) return fail(c, GNC_ERR_ARG, "shard larger than the fleet buffers were sized for (gnc_fleet_enable)");
+    fleet_params(c, &p);
+  }
   const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(c->sm_count * c->ctas_per_sm[v]));
   if (c->fleet.on) var.launch_fleet(p, grid, var.smem, stream);
   else var.launch(p, grid, var.smem, stream);
@@ -764,7 +792,9 @@ extern "C" int gnc_fleet_enable(gnc_ctx* c, uint32_t fleet_nodes_cap, void* cuda
   CUDA_TRY(c, cudaSetDevice(c->device));
   NcclApi* n = nccl_api();
   gnc_ctx::Fleet& f = c->fleet;
-  f.cap = (uint32_t)((((size_t)fleet_nodes_cap + c->world - 1) / c->world + 3) & ~(size_t)3);
+  // a shard of up to ceil(fleet_nodes_cap / world) nodes; tile records take at most 2 words per 32 nodes (the 32-node tile variant)
+  f.shard_nodes = (uint32_t)(((size_t)fleet_nodes_cap + c->world - 1) / c->world);
+  f.cap = (uint32_t)(((((size_t)f.shard_nodes + 31) / 32) * 2 + 8 + 3) & ~(size_t)3);
   f.slot_u32 = gnc::kFleetHeader + f.cap;
   f.region_bytes = ((size_t)c->world * f.slot_u32 * 4 + 255) & ~(size_t)255;
   f.bytes = 2 * f.region_bytes + 3 * (size_t)c->world * 8 + 256;
@@ -828,7 +858,7 @@ extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result*
     const size_t parity = f.epoch & 1;
     AckPtrs ap = {};
     for (int q = 0; q < c->world; q++) ap.p[q] = (unsigned long long*)(f.base[q] + 2 * f.region_bytes + 2 * (size_t)c->world * 8);
-    fleet_unpack_kernel<<<2 * c->sm_count, 256, 0, stream>>>(
+    fleet_unpack_kernel<<<2 * c->sm_count, kUnpackWarps * 32, 0, stream>>>(
         (const uint32_t*)(f.base[c->rank] + parity * f.region_bytes),
         (const unsigned long long*)(f.base[c->rank] + 2 * f.region_bytes) + parity * c->world, f.epoch, c->world, c->rank, f.slot_u32,
         f.cap, all->gpu_idx, all->out_cap, all->counts, f.unpack_done, ap);
