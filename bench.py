@@ -314,8 +314,8 @@ def run_b200(args):
                    "cache": "inputs (rows_bytes_per_rank) exceed the 126 MB L2; no flush needed",
                    "collectives": {"none": "none",
                                    "nccl": "one ncclAllGather of per-rank (counts block + compacted indices) slots, then an unpack kernel",
-                                   "fused": "none after the kernel: classify stores indices and counts into every rank's buffer over NVLink "
-                                            "(peer stores), gather = flag wait + local unpack"}[gather_kind]},
+                                   "fused": "none after the kernel: classify stores per-tile GPU-node ballots, prefixes and the counts into every "
+                                            "rank's buffer over NVLink (peer stores), gather = flag wait + local rebuild of the index list"}[gather_kind]},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": NCU_TRAFFIC_BYTES_DEFAULT_WORKLOAD if (world == 1 and n_total == FLEET_NODES) else None,
                      "traffic_source": "profiles/r01_ncu_classify_10m.txt (ncu --set full, one launch)", "peak_source": peak_src, "kernel": "gnc::classify_kernel",

@@ -117,10 +117,11 @@ int gnc_classify(gnc_ctx*, const gnc_batch* in, const gnc_result* out, void* cud
 int gnc_gather(gnc_ctx*, const gnc_result* local, const gnc_result* all, void* cuda_stream);
 
 /* Multi-GPU only, optional, collective (every rank calls it once, after gnc_create): switch the
- * context to the fused gather.  Afterwards gnc_classify also stores each GPU node's index and, at the
- * end, the counts block straight into every rank's buffer over NVLink while the kernel runs, and
- * gnc_gather (indices + counts form) only waits for the other ranks' flags and packs locally -- no
- * collective follows the kernel.  `fleet_nodes_cap` bounds the fleet's node count.  Ranks must call
+ * context to the fused gather.  Afterwards gnc_classify also stores, per tile of nodes, which of them are
+ * GPU nodes (one bit each) and how many GPU nodes precede the tile, and at the end the counts block, straight
+ * into every rank's buffer over NVLink while the kernel runs; gnc_gather (indices + counts form) only waits
+ * for the other ranks' flags and rebuilds the ordered index list locally -- no collective follows the
+ * kernel.  `fleet_nodes_cap` bounds the fleet's node count (a shard: at most its share, rounded up).  Ranks must call
  * gnc_classify and gnc_gather in step (the same number of times); up to 8 ranks on one NVLink domain.
  * Returns an error (and leaves the NCCL path in place) where peer mapping is not available. */
 int gnc_fleet_enable(gnc_ctx*, uint32_t fleet_nodes_cap, void* cuda_stream);
