@@ -68,11 +68,15 @@ def _worker(rank, world, port, n, out_dir):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_two_rank_gather_equals_single_gpu(tmp_path):
+@pytest.mark.parametrize("variant", [None, "t224", "t128", "t32"])      # the tile records of the fused gather depend on the tile size
+def test_two_rank_gather_equals_single_gpu(tmp_path, variant, monkeypatch):
     import torch.multiprocessing as mp
     from k8s_gpu_node_checker_b200 import engine, pnl, synth
     n, world = 300_001, 2
+    if variant:
+        monkeypatch.setenv("GNC_VARIANT", variant)                      # read by gnc_create in the spawned ranks
     mp.spawn(_worker, args=(world, _free_port(), n, str(tmp_path)), nprocs=world, join=True)
+    monkeypatch.delenv("GNC_VARIANT", raising=False)
     tmpl, tid = synth.fleet("g2", 77, 0, n)
     rows = synth.template_rows(tmpl)
     p = pnl.from_rows([rows[t] for t in tid])
