@@ -1109,7 +1109,7 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   const size_t o_work = take(sizeof(Work)), o_depth = take(n_chunks * 4), o_evc = take(n_chunks * 4),
                o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
                o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8),
-               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_evpack = take(n_chunks * 4), o_look = take(look_bytes), o_tilebal = take((n_tiles + 1) * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
+               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_evpack = take(n_chunks * 4), o_clist = take(n_chunks * 4), o_look = take(look_bytes), o_tilebal = take((n_tiles + 1) * 4), o_tilestart = take((n_tiles + 1) * 4), o_bt32 = take((n_tiles / 1024 + 2) * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
   if (off > c->json_scratch_bytes) {
     if (c->json_scratch) {
       CUDA_TRY(c, cudaStreamSynchronize(stream));
@@ -1133,11 +1133,12 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   mk.w = (uint4*)(base + o_masks);
   int* min_rel = (int*)(base + o_minrel);
   unsigned int* evpack = (unsigned int*)(base + o_evpack);
+  unsigned int* chunk_list = (unsigned int*)(base + o_clist);
   unsigned long long* look = (unsigned long long*)(base + o_look);
   unsigned long long* lex_state = look;
   unsigned int* ticket = (unsigned int*)(look + tiles_pad);
-  int* tile_bal = (int*)(base + o_tilebal);
-  const Depths dp{depth0, tile_bal};
+  int *tile_bal = (int*)(base + o_tilebal), *tile_start = (int*)(base + o_tilestart), *bt32 = (int*)(base + o_bt32);
+  const Depths dp{depth0, tile_start};
   uint2* desc = (uint2*)(base + o_desc);
   if (!aligned16(json)) return fail(c, GNC_ERR_ARG, "json must be 16-byte aligned");
   CUDA_TRY(c, cudaMemsetAsync(work, 0, sizeof(Work), stream));
@@ -1149,12 +1150,13 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
     // one pass: masks, per-chunk start depth (lexer state and depth travel from tile to tile by look-back)
     CUDA_TRY(c, cudaMemsetAsync(look, 0, look_bytes, stream));
     index_kernel<<<tb, kTileChunks, kTileSmem, stream>>>(json, n, mk, depth0, tile_bal, min_rel, lex_state, ticket, n_chunks);
-    scan_totals_block<int, OpAddI><<<1, 1024, 0, stream>>>(tile_bal, n_tiles, OpAddI(), 0, nullptr);  // tile balances -> tile start depths
-    events_kernel<<<cb, 256, 0, stream>>>(json, mk, dp, min_rel, evc, evpack, work, n_chunks);
+    if ((rc = device_exclusive_scan<int, OpAddI>(c, tile_bal, n_tiles, tile_start, bt32, nullptr, OpAddI(), 0, stream))) return rc;  // tile balances -> tile start depths
+    events_select_kernel<<<cb, 256, 0, stream>>>(dp, min_rel, evc, chunk_list, work, n_chunks);
+    events_kernel<<<8 * c->sm_count, 256, 0, stream>>>(json, mk, dp, chunk_list, evc, evpack, work);
     if ((rc = device_exclusive_scan<unsigned int, OpAddU>(c, evc, n_chunks, evp, btu, nullptr, OpAddU(), 0u, stream))) return rc;
     pick_items_kernel<<<1, 1, 0, stream>>>(json, n, mk, dp, evp, work, (unsigned int)std::min<unsigned long long>(nodes_cap, 0xFFFFFFFFull));
     element_starts_kernel<<<cb, 256, 0, stream>>>(json, mk, dp, evc, evpack, evp, work, elem, n_chunks);
-    c->launches += 5;
+    c->launches += 6;
   }
   const unsigned nb = (unsigned)std::max<unsigned long long>(1, (nodes_cap + 127) / 128);
   if (nodes_cap) {

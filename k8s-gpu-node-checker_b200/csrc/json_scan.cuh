@@ -53,6 +53,7 @@ struct Work {                 // device scratch, one per call
   unsigned int n_nodes;
   unsigned int status;
   unsigned int general_nodes;                     // nodes that went through the byte-serial parser
+  unsigned int n_listed;                          // chunks the events kernel has to walk
 };
 
 // The structural index: 32 bytes per 32 document bytes (group g -> w[2g], w[2g + 1]); bit i of a mask = byte 32 g + i.
@@ -365,34 +366,51 @@ __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __res
 }
 
 // ---- generic exclusive scan over n items, 1024 per block: block totals, scan of totals, apply ---------
+// In-order scan of one value per thread over a 1024-thread CTA: shuffles inside the warps, the 32 warp totals
+// through shared memory (sh[32]).  Returns the inclusive value; `excl` gets everything before this thread.
 template <class T, class Op>
-__device__ __forceinline__ T block_inclusive_scan_1024(T v, T* sh, Op op) {
-  sh[threadIdx.x] = v;
-  __syncthreads();
-  for (int d = 1; d < 1024; d <<= 1) {
-    const T t = threadIdx.x >= d ? op(sh[threadIdx.x - d], sh[threadIdx.x]) : sh[threadIdx.x];
-    __syncthreads();
-    sh[threadIdx.x] = t;
-    __syncthreads();
+__device__ __forceinline__ T block_scan_1024(T v, T* sh, Op op, T ident, T& excl) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const T t = __shfl_up_sync(0xFFFFFFFFu, v, d);
+    if (lane >= d) v = op(t, v);
   }
-  return sh[threadIdx.x];
+  T before = __shfl_up_sync(0xFFFFFFFFu, v, 1);  // inclusive value of the lane before mine
+  if (lane == 0) before = ident;
+  if (lane == 31) sh[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    T w = sh[lane];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const T t = __shfl_up_sync(0xFFFFFFFFu, w, d);
+      if (lane >= d) w = op(t, w);
+    }
+    sh[lane] = w;
+  }
+  __syncthreads();
+  const T warps_before = warp ? sh[warp - 1] : ident;
+  excl = op(warps_before, before);
+  return op(warps_before, v);
 }
 template <class T, class Op>
 __global__ void scan_block_totals(const T* __restrict__ in, unsigned long long n, T* __restrict__ totals, Op op, T ident) {
-  __shared__ T sh[1024];
+  __shared__ T sh[32];
   const unsigned long long i = blockIdx.x * 1024ull + threadIdx.x;
-  const T incl = block_inclusive_scan_1024<T, Op>(i < n ? in[i] : ident, sh, op);
+  T excl;
+  const T incl = block_scan_1024<T, Op>(i < n ? in[i] : ident, sh, op, ident, excl);
   if (threadIdx.x == 1023) totals[blockIdx.x] = incl;
 }
-// one block: thread t owns a contiguous run of the totals (order matters: composition does not commute)
+// one block: thread t owns a contiguous run of the totals (kept in order)
 template <class T, class Op>
 __global__ void scan_totals_block(T* totals, unsigned long long nb, Op op, T ident, T* grand) {
-  __shared__ T sh[1024];
+  __shared__ T sh[32];
   const unsigned long long per = (nb + 1023) / 1024, lo = min(nb, threadIdx.x * per), hi = min(nb, lo + per);
   T run = ident;
   for (unsigned long long b = lo; b < hi; b++) run = op(run, totals[b]);
-  const T incl = block_inclusive_scan_1024<T, Op>(run, sh, op);
-  T before = threadIdx.x ? sh[threadIdx.x - 1] : ident;
+  T before;
+  const T incl = block_scan_1024<T, Op>(run, sh, op, ident, before);
   if (grand && threadIdx.x == 1023) *grand = incl;
   for (unsigned long long b = lo; b < hi; b++) {
     const T t = totals[b];
@@ -403,16 +421,12 @@ __global__ void scan_totals_block(T* totals, unsigned long long nb, Op op, T ide
 template <class T, class Op>
 __global__ void scan_apply(const T* __restrict__ in, unsigned long long n, const T* __restrict__ totals, T* __restrict__ out,
                            Op op, T ident) {
-  __shared__ T sh[1024];
+  __shared__ T sh[32];
   const unsigned long long i = blockIdx.x * 1024ull + threadIdx.x;
-  block_inclusive_scan_1024<T, Op>(i < n ? in[i] : ident, sh, op);
-  // exclusive: everything before me in the block, after the block's own prefix
-  const T before = threadIdx.x ? sh[threadIdx.x - 1] : ident;
+  T before;  // everything before me in the block
+  block_scan_1024<T, Op>(i < n ? in[i] : ident, sh, op, ident, before);
   if (i < n) out[i] = op(totals[blockIdx.x], before);
 }
-struct OpCompose {
-  __device__ uint8_t operator()(uint8_t a, uint8_t b) const { return (uint8_t)compose(a, b); }
-};
 struct OpAddI {
   __device__ int operator()(int a, int b) const { return a + b; }
 };
@@ -471,41 +485,61 @@ __device__ __forceinline__ int visit_structurals(const Masks& mk, unsigned long 
   return depth;
 }
 
-// events: the '[' of every root-level array and every ',' directly inside one (depth 2 outside strings)
-__global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths dp,
-                              const int* __restrict__ min_rel, unsigned int* __restrict__ ev_count, unsigned int* __restrict__ ev_pack,
-                              Work* w, unsigned long long n_chunks) {
+// events: the '[' of every root-level array and every ',' directly inside one (depth 2 outside strings).
+// Two kernels: the first drops the chunks that lie deeper than the root levels throughout (four in five) and
+// lists the others; the second walks the listed chunks, one per thread.  (One kernel doing both ran its
+// walks at two active lanes per warp: the few chunks that matter were spread over all the warps.)
+__global__ void events_select_kernel(Depths dp, const int* __restrict__ min_rel, unsigned int* __restrict__ ev_count,
+                                     unsigned int* __restrict__ chunk_list, Work* w, unsigned long long n_chunks) {
   const unsigned long long c = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-  if (c >= n_chunks) return;
-  unsigned int cnt = 0, pack = 0;  // pack: where in the chunk the first four events are (element_starts_kernel reads it)
-  const int d0 = dp.at(c);
-  if (d0 + min_rel[c] > 2) {  // the whole chunk lies deeper than the root levels
-    ev_count[c] = 0;
-    return;
-  }
-  const unsigned long long chunk_base = c * kChunk;
-  visit_structurals(mk, c, d0, ~0ull, [&](unsigned long long pos, int kind, int d) {
-    if (kind == 0 && d == 1) {
-      if (json[pos] == '[') {
+  const bool in = c < n_chunks;
+  const bool keep = in && dp.at(c) + min_rel[c] <= 2;
+  if (in && !keep) ev_count[c] = 0;
+  // one atomic on the global counter per CTA (one per warp made 164k atomics on one address: 100 us)
+  __shared__ unsigned int s_count, s_base;
+  if (threadIdx.x == 0) s_count = 0;
+  __syncthreads();
+  const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+  const int lane = threadIdx.x & 31;
+  unsigned int at = 0;
+  if (lane == 0 && m) at = atomicAdd(&s_count, (unsigned int)__popc(m));
+  at = __shfl_sync(0xFFFFFFFFu, at, 0);
+  __syncthreads();
+  if (threadIdx.x == 0 && s_count) s_base = atomicAdd(&w->n_listed, s_count);
+  __syncthreads();
+  if (keep) chunk_list[s_base + at + __popc(m & ((1u << lane) - 1u))] = (unsigned int)c;
+}
+
+__global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths dp, const unsigned int* __restrict__ chunk_list,
+                              unsigned int* __restrict__ ev_count, unsigned int* __restrict__ ev_pack, Work* w) {
+  const unsigned int n_listed = w->n_listed;
+  for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_listed; t += gridDim.x * blockDim.x) {
+    const unsigned long long c = chunk_list[t];
+    unsigned int cnt = 0, pack = 0;  // pack: where in the chunk the first four events are (element_starts_kernel reads it)
+    const unsigned long long chunk_base = c * kChunk;
+    visit_structurals(mk, c, dp.at(c), ~0ull, [&](unsigned long long pos, int kind, int d) {
+      if (kind == 0 && d == 1) {
+        if (json[pos] == '[') {
+          if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
+          cnt++;
+          const unsigned int k = atomicAdd(&w->n_open, 1u);
+          if (k < kMaxRootArrays) w->root_open[k] = pos;
+        }
+      } else if (kind == 2 && d == 2) {
         if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
         cnt++;
-        const unsigned int k = atomicAdd(&w->n_open, 1u);
-        if (k < kMaxRootArrays) w->root_open[k] = pos;
+      } else if (kind == 1 && d == 2) {
+        if (json[pos] == ']') {
+          const unsigned int k = atomicAdd(&w->n_close, 1u);
+          if (k < kMaxRootArrays) w->root_close[k] = pos;
+        }
+      } else if (kind == 1 && d <= 0) {
+        atomicOr(&w->status, (unsigned int)ST_BAD_JSON);
       }
-    } else if (kind == 2 && d == 2) {
-      if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
-      cnt++;
-    } else if (kind == 1 && d == 2) {
-      if (json[pos] == ']') {
-        const unsigned int k = atomicAdd(&w->n_close, 1u);
-        if (k < kMaxRootArrays) w->root_close[k] = pos;
-      }
-    } else if (kind == 1 && d <= 0) {
-      atomicOr(&w->status, (unsigned int)ST_BAD_JSON);
-    }
-  });
-  ev_count[c] = cnt;
-  ev_pack[c] = pack;
+    });
+    ev_count[c] = cnt;
+    ev_pack[c] = pack;
+  }
 }
 
 // number of events strictly before byte `pos` (pos lies outside strings)
