@@ -1334,8 +1334,7 @@ constexpr int kWriteThreads = 128;
 constexpr unsigned int kWriteStage = 32768;   // bytes of rows a CTA assembles in shared memory before one coalesced copy out
 constexpr unsigned int kSpan = 1280;          // bytes of document one node's texts may span to be gathered by the whole warp
 constexpr int kGatherBatch = 4;               // nodes whose spans a warp holds in shared memory at a time (8 lanes cut each node's row)
-constexpr unsigned int kWriteSmem = kWriteStage + (kWriteThreads / 32) * kGatherBatch * kSpan + kWriteThreads * (8 + 4 + 4 + 4 + 8) +
-                                    kMaxDesc * kWriteThreads * 8;
+constexpr unsigned int kWriteSmem = kWriteStage + (kWriteThreads / 32) * kGatherBatch * kSpan + kWriteThreads * (8 + 4 + 4 + 4 + 8);  // 4 CTAs per SM
 
 // Writing pass.  A CTA's rows are one contiguous piece of the output: they are assembled in shared memory and
 // copied out coalesced.  The texts of a node (capacity keys and values, condition types and statuses)
@@ -1352,8 +1351,7 @@ __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
   uint8_t* gather = sh + kWriteStage;                                                    // [warps][kGatherBatch][kSpan]
   unsigned long long* s_lo = reinterpret_cast<unsigned long long*>(gather + (kWriteThreads / 32) * kGatherBatch * kSpan);  // [threads] span start
   uint8_t** s_rowp = reinterpret_cast<uint8_t**>(s_lo + kWriteThreads);                    // [threads] where the row is assembled
-  uint2* s_desc = reinterpret_cast<uint2*>(s_rowp + kWriteThreads);                        // [kMaxDesc][threads] the notes
-  unsigned int* s_len = reinterpret_cast<unsigned int*>(s_desc + kMaxDesc * kWriteThreads);  // [threads] span length, 0: not gathered
+  unsigned int* s_len = reinterpret_cast<unsigned int*>(s_rowp + kWriteThreads);           // [threads] span length, 0: not gathered
   int* s_shift = reinterpret_cast<int*>(s_len + kWriteThreads);                            // [threads] node start - span start
   unsigned int* s_ne = reinterpret_cast<unsigned int*>(s_shift + kWriteThreads);           // [threads] entries
   const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1437,8 +1435,6 @@ __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
   s_shift[threadIdx.x] = (int)(long long)(node_pos - span_lo);
   s_rowp[threadIdx.x] = row;
   s_ne[threadIdx.x] = gathered ? ne : 0u;
-#pragma unroll
-  for (int e = 0; e < kMaxDesc; e++) s_desc[e * kWriteThreads + threadIdx.x] = d[e];
   __syncwarp();
   uint8_t* wbuf = gather + warp * (kGatherBatch * kSpan);
   auto load16 = [&](unsigned long long at) -> uint4 {
@@ -1471,20 +1467,26 @@ __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
     }
     __syncwarp();
     {
-      // eight lanes per node: lane q of them writes entries q and q + 8
+      // eight lanes per node: lane q of them writes entries q and q + 8.  The notes stay in the owning lane's
+      // registers and are handed round by shuffles (a copy in shared memory cost a fourth CTA per SM).
       const int j = lane >> 3, q = lane & 7, node = warp * 32 + b0 + j;
       const unsigned int ne_j = s_ne[node];
+      unsigned int run = 2 + 2 * ne_j, off_a = 0, off_b = 0;  // where my entries' texts go
+      uint2 da = make_uint2(0, 0), db = make_uint2(0, 0);
+#pragma unroll
+      for (int e = 0; e < kMaxDesc; e++) {
+        uint2 de;
+        de.x = __shfl_sync(0xFFFFFFFFu, d[e].x, b0 + j);
+        de.y = __shfl_sync(0xFFFFFFFFu, d[e].y, b0 + j);
+        if ((unsigned int)e < ne_j) {
+          if (e == q) da = de, off_a = run;
+          if (e == q + 8) db = de, off_b = run;
+          run += ((de.y >> 16) & 0xFFu) + (de.y >> 24);
+        }
+      }
       if (ne_j) {
         uint8_t* rowp = s_rowp[node];
         const uint8_t* src = wbuf + j * kSpan + s_shift[node];  // src[x] = document byte (node start + x)
-        unsigned int run = 2 + 2 * ne_j, off_a = 0, off_b = 0;  // where my entries' texts go
-        uint2 da = make_uint2(0, 0), db = make_uint2(0, 0);
-        for (unsigned int e = 0; e < ne_j; e++) {
-          const uint2 de = s_desc[e * kWriteThreads + node];
-          if (e == (unsigned int)q) da = de, off_a = run;
-          if (e == (unsigned int)q + 8) db = de, off_b = run;
-          run += ((de.y >> 16) & 0xFFu) + (de.y >> 24);
-        }
         auto put = [&](unsigned int e, uint2 de, unsigned int text_off) {
           const unsigned int kl = (de.y >> 16) & 0xFFu, vl = de.y >> 24;
           const unsigned int vt = kl ? de.x + (int)(short)(de.y & 0xFFFFu) : de.x;
