@@ -29,7 +29,7 @@ sys.path.insert(0, ROOT)
 FLEET_NODES = 10_000_000
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE classify launch on the default workload (N=1), from the
 # `ncu --set full` capture summarised in profiles/r01_ncu_classify_10m.txt (2.1139 GB read + 0.2978 GB written)
-NCU_TRAFFIC_BYTES_DEFAULT_WORKLOAD = 2_411_719_512
+NCU_TRAFFIC_BYTES_DEFAULT_WORKLOAD = 2_411_907_392
 METRIC = "node_records_per_sec"
 UNIT = "nodes/s"
 WORKLOAD = "g1-10M-node synthetic NodeList (BASELINE.json configs[2]; seed 0)"
