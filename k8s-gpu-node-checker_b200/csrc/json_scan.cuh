@@ -1340,8 +1340,9 @@ constexpr unsigned int kWriteSmem = kWriteStage + (kWriteThreads / 32) * kGather
 // copied out coalesced.  The texts of a node (capacity keys and values, condition types and statuses)
 // lie within about a kilobyte of the document; the measuring pass noted where.  A thread fetching its own
 // node's texts one after another waits a memory round trip for each, so the warp fetches them together:
-// for eight nodes at a time all 32 lanes copy the nodes' spans into shared memory with independent 16-byte
-// loads, then the eight owning lanes cut their rows out of shared memory.
+// for four nodes at a time all 32 lanes copy the nodes' spans into shared memory with independent 16-byte
+// loads (all issued before the first is used), then eight lanes per node cut its row out of shared memory.
+// The pass is latency-bound: shared memory is kept to 55.5 KB per CTA so that four CTAs fit an SM.
 __global__ void __launch_bounds__(kWriteThreads) write_rows_kernel(
     const uint8_t* __restrict__ json, unsigned long long n, Masks mk, const NodePlan* __restrict__ plans, const uint2* __restrict__ desc,
     const unsigned long long* __restrict__ elem_pos, const Work* w, const unsigned int* __restrict__ sizes,
