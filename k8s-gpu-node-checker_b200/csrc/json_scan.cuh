@@ -90,6 +90,8 @@ __device__ __forceinline__ uint32_t eq_bytes(uint32_t w, uint32_t k4) {
 }
 // the four 0x80 flags of z as a nibble, byte 0 in bit 0 (the partial products never collide)
 __device__ __forceinline__ uint32_t flags_to_nibble(uint32_t z) { return (z * 0x00204081u) >> 28; }
+// the same nibble left in the top four bits (the other bits cleared)
+__device__ __forceinline__ uint32_t flags_to_top_nibble(uint32_t z) { return (z * 0x00204081u) & 0xF0000000u; }
 
 struct RawMasks {
   uint32_t q, b, o, c, k;
@@ -101,8 +103,8 @@ __device__ __forceinline__ void raw_quotes(const uint32_t* __restrict__ w, RawMa
 #pragma unroll 2
   for (int i = 0; i < 8; i++) {
     const uint32_t x = w[i];
-    q |= flags_to_nibble(eq_bytes(x, 0x22222222u)) << (4 * i);
-    b |= flags_to_nibble(eq_bytes(x, 0x5C5C5C5Cu)) << (4 * i);
+    q = (q >> 4) | flags_to_top_nibble(eq_bytes(x, 0x22222222u));  // after eight words the first word's nibble is at bit 0
+    b = (b >> 4) | flags_to_top_nibble(eq_bytes(x, 0x5C5C5C5Cu));
   }
   m.q = q, m.b = b;
 }
@@ -112,9 +114,9 @@ __device__ __forceinline__ void raw_brackets(const uint32_t* __restrict__ w, Raw
 #pragma unroll 2
   for (int i = 0; i < 8; i++) {
     const uint32_t x = w[i], folded = x & 0xDFDFDFDFu;  // '{' -> '[', '}' -> ']' (nothing else lands on them)
-    o |= flags_to_nibble(eq_bytes(folded, 0x5B5B5B5Bu)) << (4 * i);
-    c |= flags_to_nibble(eq_bytes(folded, 0x5D5D5D5Du)) << (4 * i);
-    k |= flags_to_nibble(eq_bytes(x, 0x2C2C2C2Cu)) << (4 * i);
+    o = (o >> 4) | flags_to_top_nibble(eq_bytes(folded, 0x5B5B5B5Bu));
+    c = (c >> 4) | flags_to_top_nibble(eq_bytes(folded, 0x5D5D5D5Du));
+    k = (k >> 4) | flags_to_top_nibble(eq_bytes(x, 0x2C2C2C2Cu));
   }
   m.o = o, m.c = c, m.k = k;
 }
@@ -510,35 +512,76 @@ __global__ void events_select_kernel(Depths dp, const int* __restrict__ min_rel,
   if (keep) chunk_list[s_base + at + __popc(m & ((1u << lane) - 1u))] = (unsigned int)c;
 }
 
+// Thread per listed chunk.  First every group's start depth by popcount (no branches), which also tells
+// which groups can touch the root levels -- one or two of the eight; then a loop whose iteration is "my next
+// such group", so that lanes whose interesting groups sit at different places in their chunks still walk them
+// together (a loop over the eight groups with the bit walk inside ran each lane's walk on its own).
 __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths dp, const unsigned int* __restrict__ chunk_list,
                               unsigned int* __restrict__ ev_count, unsigned int* __restrict__ ev_pack, Work* w) {
   const unsigned int n_listed = w->n_listed;
-  for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_listed; t += gridDim.x * blockDim.x) {
-    const unsigned long long c = chunk_list[t];
+  for (unsigned int t0 = blockIdx.x * blockDim.x; t0 < n_listed; t0 += gridDim.x * blockDim.x) {  // whole warps stay in the loop
+    const unsigned int t = t0 + threadIdx.x;
+    const bool have = t < n_listed;
+    const unsigned long long c = have ? chunk_list[t] : 0;
+    const uint4* pw = mk.w + c * (2 * kGroupsPerChunk);
+    const int d0 = have ? dp.at(c) : 0;
+    // pass 1: depth at the start of each group, relative to d0, packed as eight int16; which groups come near the root
+    uint32_t rel[4] = {0, 0, 0, 0}, near = 0;
+    int bal = 0;
+    if (have) {
+#pragma unroll
+      for (int g = 0; g < kGroupsPerChunk; g++) {
+        const uint4 a = __ldg(pw + 2 * g);
+        rel[g >> 1] |= ((uint32_t)bal & 0xFFFFu) << (16 * (g & 1));
+        if (d0 + bal - __popc(a.w) <= 2) near |= 1u << g;
+        bal += __popc(a.z) - __popc(a.w);
+      }
+    }
     unsigned int cnt = 0, pack = 0;  // pack: where in the chunk the first four events are (element_starts_kernel reads it)
     const unsigned long long chunk_base = c * kChunk;
-    visit_structurals(mk, c, dp.at(c), ~0ull, [&](unsigned long long pos, int kind, int d) {
-      if (kind == 0 && d == 1) {
-        if (json[pos] == '[') {
+    while (__any_sync(0xFFFFFFFFu, near != 0)) {
+      if (near == 0) continue;
+      const int g = __ffs(near) - 1;
+      near &= near - 1;
+      const uint32_t r2 = g < 2 ? rel[0] : g < 4 ? rel[1] : g < 6 ? rel[2] : rel[3];
+      int depth = d0 + (int)(short)((r2 >> (16 * (g & 1))) & 0xFFFFu);
+      const uint4 a = __ldg(pw + 2 * g);
+      const uint32_t o = a.z, cl = a.w, k = __ldg(reinterpret_cast<const uint32_t*>(pw + 2 * g + 1));
+      const unsigned long long base = chunk_base + (unsigned long long)g * kGroup;
+      uint32_t any = o | cl | k;
+      while (any) {
+        const int bit = __ffs(any) - 1;
+        const uint32_t bm = 1u << bit;
+        const unsigned long long pos = base + bit;
+        any &= any - 1;
+        if (o & bm) {
+          if (depth == 1 && json[pos] == '[') {
+            if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
+            cnt++;
+            const unsigned int q = atomicAdd(&w->n_open, 1u);
+            if (q < kMaxRootArrays) w->root_open[q] = pos;
+          }
+          depth++;
+        } else if (cl & bm) {
+          if (depth == 2) {
+            if (json[pos] == ']') {
+              const unsigned int q = atomicAdd(&w->n_close, 1u);
+              if (q < kMaxRootArrays) w->root_close[q] = pos;
+            }
+          } else if (depth <= 0) {
+            atomicOr(&w->status, (unsigned int)ST_BAD_JSON);
+          }
+          depth--;
+        } else if (depth == 2) {
           if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
           cnt++;
-          const unsigned int k = atomicAdd(&w->n_open, 1u);
-          if (k < kMaxRootArrays) w->root_open[k] = pos;
         }
-      } else if (kind == 2 && d == 2) {
-        if (cnt < 4) pack |= (unsigned int)(pos - chunk_base) << (8 * cnt);
-        cnt++;
-      } else if (kind == 1 && d == 2) {
-        if (json[pos] == ']') {
-          const unsigned int k = atomicAdd(&w->n_close, 1u);
-          if (k < kMaxRootArrays) w->root_close[k] = pos;
-        }
-      } else if (kind == 1 && d <= 0) {
-        atomicOr(&w->status, (unsigned int)ST_BAD_JSON);
       }
-    });
-    ev_count[c] = cnt;
-    ev_pack[c] = pack;
+    }
+    if (have) {
+      ev_count[c] = cnt;
+      ev_pack[c] = pack;
+    }
   }
 }
 
