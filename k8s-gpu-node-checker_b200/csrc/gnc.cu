@@ -1103,7 +1103,7 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
   const size_t nbc = (n_chunks + 1023) / 1024 + 1, nbn = (nodes_cap + 1023) / 1024 + 1;
-  const size_t mask_bytes = (size_t)n_chunks * kChunk;  // the structural index: one byte per document byte
+  const size_t mask_bytes = (size_t)n_chunks * kChunk / 2;  // the structural index: 16 bytes per 32 document bytes
   const size_t n_tiles = (n_chunks + kTileChunks - 1) / kTileChunks, tiles_pad = align_up(n_tiles + 1, kLookWindow);
   const size_t look_bytes = tiles_pad * 8 + 256;  // lexer look-back states, then the tile ticket
   const size_t o_work = take(sizeof(Work)), o_depth = take(n_chunks * 4), o_evc = take(n_chunks * 4),

@@ -56,13 +56,18 @@ struct Work {                 // device scratch, one per call
   unsigned int n_listed;                          // chunks the events kernel has to walk
 };
 
-// The structural index: 32 bytes per 32 document bytes (group g -> w[2g], w[2g + 1]); bit i of a mask = byte 32 g + i.
-//   w[2g]     = { opening quotes, closing quotes, '{' '[' outside strings, '}' ']' outside strings }
-//   w[2g + 1] = { ',' outside strings, backslashes inside strings, 0, 0 }
-// One 32-byte sector per group: the node walkers, one thread per node at scattered places, fetch every sector once.
+// The structural index: one 16-byte record per 32 document bytes (group g -> w[g]); bit i of a word = byte 32 g + i.
+//   { p0, p1, p2, backslashes inside strings }: p2 p1 p0 at a bit spell the kind of structural byte there --
+//   1 opening quote, 2 closing quote, 3 '{' '[', 4 '}' ']', 5 ','  (brackets and commas outside strings only); 0: none.
+// Kinds as bit planes rather than one mask per kind: the walkers' "next structural byte" is one OR of three
+// words and three bit tests instead of an OR of five and a five-way select, and the index is half the bytes.
 struct Masks {
   uint4* w;
 };
+__device__ __forceinline__ uint32_t plane_open(const uint4 a) { return a.x & a.y; }          // kind 3
+__device__ __forceinline__ uint32_t plane_close(const uint4 a) { return a.z & ~a.x; }        // kind 4
+__device__ __forceinline__ uint32_t plane_comma(const uint4 a) { return a.z & a.x; }         // kind 5
+__device__ __forceinline__ uint32_t plane_str_open(const uint4 a) { return a.x & ~a.y & ~a.z; }  // kind 1
 
 // Depth (brackets open outside strings) at the start of a chunk = depth inside its tile + the tile's start depth.
 struct Depths {
@@ -330,15 +335,15 @@ __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __res
   uint32_t pe = st & 1u, in_str = (st >> 1) ? 0xFFFFFFFFu : 0u;
   int bal = 0, low = 0;
   if (have) {
-    uint4* out = mk.w + c * (2 * kGroupsPerChunk);
+    uint4* out = mk.w + c * kGroupsPerChunk;
 #pragma unroll
     for (int g = 0; g < kGroupsPerChunk; g++) {
       const uint32_t q = m[g].q & ~escaped_bytes(m[g].b, pe);
       const uint32_t s = prefix_xor(q) ^ in_str;  // bit i: byte i is inside a string (opening quote included, closing quote not)
       in_str = (s >> 31) ? 0xFFFFFFFFu : 0u;
       const uint32_t o = m[g].o & ~s, cl = m[g].c & ~s;
-      out[2 * g] = make_uint4(q & s, q & ~s, o, cl);
-      out[2 * g + 1] = make_uint4(m[g].k & ~s, m[g].b & s, 0u, 0u);
+      const uint32_t so = q & s, sc = q & ~s, k = m[g].k & ~s;
+      out[g] = make_uint4(so | o | k, sc | o, cl | k, m[g].b & s);
       low = min(low, bal - __popc(cl));  // as if every close of the group came first
       bal += __popc(o) - __popc(cl);
     }
@@ -447,13 +452,12 @@ struct OpAddULL {
 // branches for the same few bits.)
 template <class F>
 __device__ __forceinline__ int visit_structurals(const Masks& mk, unsigned long long c, int depth, unsigned long long limit, F&& f) {
-  const uint4* pw = mk.w + c * (2 * kGroupsPerChunk);
+  const uint4* pw = mk.w + c * kGroupsPerChunk;
   uint32_t ow[8], cw[8], kw[8];
 #pragma unroll
   for (int g = 0; g < kGroupsPerChunk; g++) {
-    const uint4 a = __ldg(pw + 2 * g);
-    ow[g] = a.z, cw[g] = a.w;
-    kw[g] = __ldg(reinterpret_cast<const uint32_t*>(pw + 2 * g + 1));
+    const uint4 a = __ldg(pw + g);
+    ow[g] = plane_open(a), cw[g] = plane_close(a), kw[g] = plane_comma(a);
   }
 #pragma unroll
   for (int g = 0; g < kGroupsPerChunk; g++) {
@@ -523,7 +527,7 @@ __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths
     const unsigned int t = t0 + threadIdx.x;
     const bool have = t < n_listed;
     const unsigned long long c = have ? chunk_list[t] : 0;
-    const uint4* pw = mk.w + c * (2 * kGroupsPerChunk);
+    const uint4* pw = mk.w + c * kGroupsPerChunk;
     const int d0 = have ? dp.at(c) : 0;
     // pass 1: depth at the start of each group, relative to d0, packed as eight int16; which groups come near the root
     uint32_t rel[4] = {0, 0, 0, 0}, near = 0;
@@ -531,10 +535,11 @@ __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths
     if (have) {
 #pragma unroll
       for (int g = 0; g < kGroupsPerChunk; g++) {
-        const uint4 a = __ldg(pw + 2 * g);
+        const uint4 a = __ldg(pw + g);
+        const int closes = __popc(plane_close(a));
         rel[g >> 1] |= ((uint32_t)bal & 0xFFFFu) << (16 * (g & 1));
-        if (d0 + bal - __popc(a.w) <= 2) near |= 1u << g;
-        bal += __popc(a.z) - __popc(a.w);
+        if (d0 + bal - closes <= 2) near |= 1u << g;
+        bal += __popc(plane_open(a)) - closes;
       }
     }
     unsigned int cnt = 0, pack = 0;  // pack: where in the chunk the first four events are (element_starts_kernel reads it)
@@ -545,8 +550,8 @@ __global__ void events_kernel(const uint8_t* __restrict__ json, Masks mk, Depths
       near &= near - 1;
       const uint32_t r2 = g < 2 ? rel[0] : g < 4 ? rel[1] : g < 6 ? rel[2] : rel[3];
       int depth = d0 + (int)(short)((r2 >> (16 * (g & 1))) & 0xFFFFu);
-      const uint4 a = __ldg(pw + 2 * g);
-      const uint32_t o = a.z, cl = a.w, k = __ldg(reinterpret_cast<const uint32_t*>(pw + 2 * g + 1));
+      const uint4 a = __ldg(pw + g);
+      const uint32_t o = plane_open(a), cl = plane_close(a), k = plane_comma(a);
       const unsigned long long base = chunk_base + (unsigned long long)g * kGroup;
       uint32_t any = o | cl | k;
       while (any) {
@@ -1018,7 +1023,7 @@ __global__ void pick_items_kernel(const uint8_t* __restrict__ json, unsigned lon
     // compared decoded, so that an escaped spelling of "items" counts as json.loads counts it.
     long long open = -1;
     for (long long g = i >> 5; g >= 0 && open < 0; g--) {
-      uint32_t so = mk.w[2 * g].x;
+      uint32_t so = plane_str_open(mk.w[g]);
       if (g == (i >> 5)) so &= (1u << (unsigned)(i & 31)) - 1u;
       if (so) open = (g << 5) + (31 - __clz(so));
     }
@@ -1105,57 +1110,50 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
   const bool idle = g0 >= g_end || top < 0;
   const unsigned long long base0 = g0 << 5;               // document position of relative position 0
   const uint32_t rel0 = (uint32_t)(pos & 31);             // relative position of the start of the walk
-  const uint4* wp = mk.w + (idle ? 0 : 2 * g0);           // the current group's masks
+  const uint4* wp = mk.w + (idle ? 0 : g0);               // the current group's record
   uint32_t left = idle ? 0u : (uint32_t)min(g_end - g0 - 1, 0x03FFFFFFull);  // groups that may still follow (2 GiB per walk)
   uint32_t gr = 0;                                        // current group, relative
-  uint32_t so = 0, sc = 0, op = 0, cl = 0, cm = 0, bk = 0;
+  uint32_t p0 = 0, p1 = 0, p2 = 0, bk = 0;                // kind planes and backslashes of the group, bits not yet consumed
   uint4 na = make_uint4(0, 0, 0, 0);                      // the next group, fetched ahead
-  uint2 nb = make_uint2(0, 0);
   if (!idle) {
     const uint4 a = __ldg(wp);
-    const uint2 b = __ldg(reinterpret_cast<const uint2*>(wp + 1));
     const uint32_t keep = ~0u << rel0;
-    so = a.x & keep, sc = a.y & keep, op = a.z & keep, cl = a.w & keep, cm = b.x & keep, bk = b.y & keep;
-    if (left) {
-      na = __ldg(wp + 2);
-      nb = __ldg(reinterpret_cast<const uint2*>(wp + 3));
-    }
+    p0 = a.x & keep, p1 = a.y & keep, p2 = a.z & keep, bk = a.w & keep;
+    if (left) na = __ldg(wp + 1);
   }
   bool ended = false;   // ran off the document
   uint32_t bacc = 0;    // backslashes passed since the last opening quote
   auto advance = [&]() {
     if (left == 0) {
       ended = true;
-      so = sc = op = cl = cm = bk = 0;
+      p0 = p1 = p2 = bk = 0;
       return;
     }
-    --left, ++gr, wp += 2;
+    --left, ++gr, ++wp;
     bacc |= bk;
-    so = na.x, sc = na.y, op = na.z, cl = na.w, cm = nb.x, bk = nb.y;
-    if (left) {
-      na = __ldg(wp + 2);
-      nb = __ldg(reinterpret_cast<const uint2*>(wp + 3));
-    }
+    p0 = na.x, p1 = na.y, p2 = na.z, bk = na.w;
+    if (left) na = __ldg(wp + 1);
   };
   // the next structural byte: its kind, its relative position in `at`; -1 at the end of the document
   auto next = [&](uint32_t& at) -> int {
     uint32_t any;
-    while ((any = so | sc | op | cl | cm) == 0) {
+    while ((any = p0 | p1 | p2) == 0) {
       advance();
       if (ended) return -1;
     }
     const int bit = __ffs(any) - 1;
-    const uint32_t bm = 1u << bit, keep = ~((bm << 1) - 1u);
+    const uint32_t keep = ~((2u << bit) - 1u);
     at = (gr << 5) + bit;
-    const int kind = (so & bm) ? SK_STR_OPEN : (sc & bm) ? SK_STR_CLOSE : (op & bm) ? SK_OPEN : (cl & bm) ? SK_CLOSE : SK_COMMA;
+    const int kind = (int)(((p0 >> bit) & 1u) | (((p1 >> bit) & 1u) << 1) | (((p2 >> bit) & 1u) << 2)) - 1;  // the planes spell kind + 1
     bacc = kind == SK_STR_OPEN ? 0u : (bacc | (bk & ~keep));  // at a closing quote: non-zero iff the string held a backslash
-    so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep, bk &= keep;
+    p0 &= keep, p1 &= keep, p2 &= keep, bk &= keep;
     return kind;
   };
   // the opening bracket has just been consumed: pass its container, whole groups at a time where it cannot close
   auto skip_container = [&]() -> bool {
     int depth = 1;
     while (true) {
+      const uint32_t op = p0 & p1, cl = p2 & ~p0;  // kinds 3 and 4
       if (__popc(cl) < depth) {
         depth += __popc(op) - __popc(cl);
       } else {
@@ -1167,7 +1165,7 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
             depth++;
           } else if (--depth == 0) {
             const uint32_t keep = ~((2u << bit) - 1u);
-            so &= keep, sc &= keep, op &= keep, cl &= keep, cm &= keep, bk &= keep;
+            p0 &= keep, p1 &= keep, p2 &= keep, bk &= keep;
             return true;
           }
         }
