@@ -12,8 +12,9 @@
 //               compares; each chunk's effect on the lexer state {escape pending, inside string} as a
 //               transition function, scanned inside the CTA and carried from tile to tile by decoupled
 //               look-back.  With the start state known: escaped bytes, unescaped quotes, in-string mask
-//               (prefix xor), and six masks per group -- string opens, string closes, brackets open /
-//               close outside strings, commas outside strings, backslashes inside strings -- plus every
+//               (prefix xor), and per group the kind of every structural byte -- string open, string
+//               close, bracket open / close and comma outside strings -- as three bit planes, plus the
+//               backslashes inside strings (16 bytes per 32 document bytes), plus every
 //               chunk's start depth relative to its tile; a small kernel scans the tiles' bracket balances
 //   2. events:  element separators of root-level arrays (the '[' itself and each ',' at depth 2) are
 //               counted per chunk from the masks and scanned; root-level array brackets are listed; one
@@ -263,7 +264,7 @@ __device__ uint32_t tile_resolve(unsigned long long* st, int t, uint32_t mine, i
   return acc;
 }
 
-// The six masks of every group, every chunk's depth at its start and a lower bound of the depth inside it.
+// The index record of every group, every chunk's depth at its start (relative to the tile) and a lower bound of the depth inside it.
 __global__ void __launch_bounds__(kTileChunks) index_kernel(const uint8_t* __restrict__ json, unsigned long long n, Masks mk,
                                                             int* __restrict__ depth_local, int* __restrict__ tile_bal,
                                                             int* __restrict__ min_rel, unsigned long long* lex_state,
