@@ -240,3 +240,31 @@ def test_elements_that_are_not_objects_and_odd_values(clf):
              '{"status":{"conditions":[{"type":"Ready","status":"True","extra":{"a":[1,2,{"b":"}"}]}}],"capacity":{"amd.com/gpu":"2"}}}',
              '{"spec":{"taints":[{"key":"k","value":null}]},"status":{"capacity":{"":"5","nvidia.com/gpu":""},"conditions":[{"type":"","status":""}]}}']
     _check_rows(clf, _doc(nodes), len(nodes))
+
+
+def test_backslash_runs_and_long_strings_across_block_boundaries(clf):
+    """The lexer's carries: runs of backslashes of every length and parity, quotes after them, and strings of
+    hundreds of kilobytes, slid across the 32-byte group, 256-byte chunk and 32 KB tile boundaries by padding."""
+    import random
+    r = random.Random(5)
+    nodes = []
+    for i in range(400):
+        k = r.choice([1, 2, 3, 15, 16, 17, 31, 32, 33, 63, 64, 65, 127, 128, 255, 256, 257, 300])
+        junk = ("\\" * k) + r.choice(['"', '', 'x', '"}]', '\\"']) + ("\\" * r.randint(0, 3))
+        pad = " " * r.randint(0, 70)
+        ann = json.dumps({"a": junk, "b": ["\\", "\"", junk[::-1]], pad + "k": junk + '"'})
+        gpus = str(1 + i % 8)
+        nodes.append('{"metadata":{"annotations":%s,"name":%s},%s"status":{"capacity":{"nvidia.com/gpu":"%s","cpu":"8"},'
+                     '"conditions":[{"message":%s,"type":"Ready","status":"%s"}]}}'
+                     % (ann, json.dumps("n" + junk), pad, gpus, json.dumps(junk), "True" if i % 3 else "False"))
+    big = json.dumps(("\\\"" * 40000) + "}{][,:" * 20000)                      # ~360 KB of escapes and brackets in one string
+    nodes.insert(200, '{"metadata":{"annotations":{"big":%s}},"status":{"capacity":{"amd.com/gpu":"2"},"conditions":[]}}' % big)
+    nodes.insert(300, '{"status":{"capacity":{"intel.com/gpu":%s},"conditions":[{"type":"Ready","status":"True"}]}}' % json.dumps("7" * 70000))
+    doc = _doc(nodes)
+    for shift in (0, 1, 13, 31):
+        d = (b" " * shift) + doc
+        json.loads(d)
+        batch, got = _device_classify(clf, d, len(nodes) + 8)
+        nodes_o, p, ora = _oracle_classify(d)
+        assert batch.n_nodes == len(nodes_o) == len(nodes)
+        assert_same_outputs(got, ora, f"shift {shift}")
