@@ -1150,6 +1150,21 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
     p0 &= keep, p1 &= keep, p2 &= keep, bk &= keep;
     return kind;
   };
+  // the next bracket or comma, strings passed over unseen (the planes hold nothing for the bytes inside them): how a
+  // member whose key does not matter is left behind in one step instead of three
+  auto next_delim = [&](uint32_t& at) -> int {
+    uint32_t any;
+    while ((any = (p0 & p1) | p2) == 0) {
+      advance();
+      if (ended) return -1;
+    }
+    const int bit = __ffs(any) - 1;
+    const uint32_t keep = ~((2u << bit) - 1u);
+    at = (gr << 5) + bit;
+    const int kind = ((p2 >> bit) & 1u) ? (((p0 >> bit) & 1u) ? SK_COMMA : SK_CLOSE) : SK_OPEN;
+    p0 &= keep, p1 &= keep, p2 &= keep, bk &= keep;
+    return kind;
+  };
   // the opening bracket has just been consumed: pass its container, whole groups at a time where it cannot close
   auto skip_container = [&]() -> bool {
     int depth = 1;
@@ -1242,7 +1257,8 @@ __device__ bool fast_walk(const uint8_t* __restrict__ json, unsigned long long n
           continue;
         }
       }
-      kind = next(at);  // the first structural byte of the value
+      // the first structural byte of the value; for a member that cannot matter, the delimiter that ends it
+      kind = (level != L_CAP && key == KEY_OTHER) ? next_delim(at) : next(at);
     }
     if (!pop) {
       // ---- the value (or array element): `kind` at `at` is its first structural byte ----
