@@ -1106,10 +1106,23 @@ extern "C" int gnc_json_to_pnl(gnc_ctx* c, const uint8_t* json, uint64_t json_by
   const size_t mask_bytes = (size_t)n_chunks * kChunk / 2;  // the structural index: 16 bytes per 32 document bytes
   const size_t n_tiles = (n_chunks + kTileChunks - 1) / kTileChunks, tiles_pad = align_up(n_tiles + 1, kLookWindow);
   const size_t look_bytes = tiles_pad * 8 + 256;  // lexer look-back states, then the tile ticket
-  const size_t o_work = take(sizeof(Work)), o_depth = take(n_chunks * 4), o_evc = take(n_chunks * 4),
-               o_evp = take(n_chunks * 4), o_btu = take(nbc * 4), o_elem = take((nodes_cap + 1) * 8), o_sizes = take((nodes_cap + 1) * 4),
-               o_plain = take((nodes_cap + 1) * 8), o_plans = take((nodes_cap + 1) * sizeof(NodePlan)), o_offs = take((nodes_cap + 1) * 8), o_bt64 = take(nbn * 8), o_total = take(8),
-               o_masks = take(mask_bytes), o_minrel = take(n_chunks * 4), o_evpack = take(n_chunks * 4), o_clist = take(n_chunks * 4), o_look = take(look_bytes), o_tilebal = take((n_tiles + 1) * 4), o_tilestart = take((n_tiles + 1) * 4), o_bt32 = take((n_tiles / 1024 + 2) * 4), o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));
+  // per chunk (256 document bytes)
+  const size_t o_work = take(sizeof(Work));
+  const size_t o_masks = take(mask_bytes);                 // the index
+  const size_t o_depth = take(n_chunks * 4);               // start depth relative to the tile
+  const size_t o_minrel = take(n_chunks * 4);              // lower bound of the depth inside the chunk
+  const size_t o_evc = take(n_chunks * 4), o_evp = take(n_chunks * 4), o_btu = take(nbc * 4);  // events: counts, prefix, block totals
+  const size_t o_evpack = take(n_chunks * 4);              // places of a chunk's first four events
+  const size_t o_clist = take(n_chunks * 4);               // chunks the events kernel walks
+  // per tile (128 chunks)
+  const size_t o_look = take(look_bytes);
+  const size_t o_tilebal = take((n_tiles + 1) * 4), o_tilestart = take((n_tiles + 1) * 4), o_bt32 = take((n_tiles / 1024 + 2) * 4);
+  // per node
+  const size_t o_elem = take((nodes_cap + 1) * 8);         // where each element of items starts
+  const size_t o_sizes = take((nodes_cap + 1) * 4), o_plain = take((nodes_cap + 1) * 8), o_offs = take((nodes_cap + 1) * 8);
+  const size_t o_bt64 = take(nbn * 8), o_total = take(8);
+  const size_t o_plans = take((nodes_cap + 1) * sizeof(NodePlan));
+  const size_t o_desc = take((nodes_cap + 1) * (size_t)kMaxDesc * sizeof(uint2));  // the measuring pass's notes
   if (off > c->json_scratch_bytes) {
     if (c->json_scratch) {
       CUDA_TRY(c, cudaStreamSynchronize(stream));
