@@ -142,8 +142,11 @@ int gnc_classify_host(gnc_ctx*, const gnc_batch* host_in, const gnc_result* host
  * are large (down to 32 per tile, 2M nodes); a larger shard is refused with GNC_ERR_ARG and a text
  * saying so.  Inputs and outputs are the caller's DEVICE buffers, exactly as for gnc_classify;
  * max_str_digits is sys.get_int_max_str_digits() (4300 by default, 0 = no limit).
- *  - The first call on each device looks up the array's device address and the launch geometry.
- *    Make that call outside any stream capture.
+ *  - The first call on each device looks up the array's device address and the launch geometry.  If the
+ *    process has not used that device yet, this is also when the CUDA runtime creates its context and
+ *    loads this library's module, i.e. when the array and the kernel images take up their device memory:
+ *    make that call early, before the memory budget is spent, and outside any stream capture.
+ *  - Host threads may call concurrently (the set-up and launch are serialised by a lock inside).
  *  - All calls on a device share the one array, which keeps the previous call's contents; each call
  *    clears what has to start from zero, on `cuda_stream`.  Two calls whose kernels overlap on the
  *    GPU (different streams, different threads) race on it: order them.
@@ -157,9 +160,10 @@ int gnc_classify_static(int device, const gnc_batch* in, const gnc_result* out, 
  * Stands where the reference lets the kubernetes client fetch and deserialise the NodeList
  * (api.list_node().items, check-gpu-node.py:217): only what the path reads is extracted -- each item's
  * status.capacity entries (:183-187) and the type/status of its status.conditions (:173-177) -- with
- * json.loads semantics (last duplicate key wins, \uXXXX escapes, surrogate pairs).  Non-string capacity
- * values follow the client's dict(str,str) conversion: numbers keep their token (zero is falsy, skipped),
- * true/false/null/containers never survive int(str(.)).  Asynchronous on `cuda_stream`.
+ * json.loads semantics (last duplicate key wins, \uXXXX escapes, surrogate pairs).  Non-string scalars
+ * follow the client's str() conversion of declared-'str' fields: an integer token is its own text (zero,
+ * "0" or "-0", is "0": kept, value 0), floats / true / false / containers never survive int(str(.)), null
+ * stays None; a condition's `status: true` is "True".  Asynchronous on `cuda_stream`.
  * info[0] nodes, info[1] rows_bytes (= row_ptr[nodes]), info[2] status bits (1 no root "items" array,
  * 2 nodes_cap too small, 4 rows_cap too small, 8 unbalanced JSON, 16 too many root-level arrays),
  * info[3]/[4] byte positions of the items array's brackets, info[5] how many nodes needed the general
@@ -176,6 +180,10 @@ int gnc_json_to_pnl(gnc_ctx*, const uint8_t* json, uint64_t json_bytes, const gn
 
 /* Kernels this context has launched since it was created (for benchmark accounting). */
 uint64_t gnc_launch_count(const gnc_ctx*);
+
+/* Name of the kernel variant (nodes per tile, e.g. "t224") gnc_classify picks for a shard of this shape when
+ * GNC_VARIANT is not set; profiles and benchmark lines name it so that a capture is matched to the code it measured. */
+const char* gnc_variant_for(uint64_t rows_bytes, uint32_t n_nodes);
 
 /* Unicode tables the quantity parser was built with (decimal-digit run starts, wide spaces). */
 int gnc_unicode_tables(const uint32_t** nd_runs, int* n_runs, const uint32_t** spaces, int* n_spaces);

@@ -43,8 +43,21 @@ def _payload(node: Any) -> Tuple[str, Dict, List]:
     return (md.name if md else ""), (md.labels if md and md.labels else {}), taints
 
 
-def build_records(nodes: Sequence[Any], res: engine.FleetResult) -> Tuple[List[Dict], List[Dict]]:
-    """(gpu_nodes, ready_gpu_nodes) from the device's decisions plus each node's payload."""
+def _native_args(res: engine.FleetResult):
+    """FleetResult -> the buffers csrc/fastpack.c reads (bignum nodes travel in `wide`)."""
+    wide = {n: (sum(bd.values()), bd) for n, bd in res.wide.items()} if res.wide else None
+    totals = np.array([t if -2 ** 63 <= t < 2 ** 63 else 0 for t in res.gpu_total], dtype=np.int64) \
+        if res.wide else np.asarray(res.gpu_total, dtype=np.int64)
+    return (np.ascontiguousarray(res.gpu_idx, dtype=np.int64), np.ascontiguousarray(res.flags), totals,
+            np.ascontiguousarray(res.gpu_vals, dtype=np.int64).reshape(-1), wide, res.node_base)
+
+
+def build_records(nodes: Sequence[Any], res: engine.FleetResult, use_c: Optional[bool] = None) -> Tuple[List[Dict], List[Dict]]:
+    """(gpu_nodes, ready_gpu_nodes) from the device's decisions plus each node's payload
+    (check-gpu-node.py:202-212, :222-225).  The C extension builds the dicts when it is there."""
+    fp = pnl._fastpack() if use_c is not False else None
+    if fp is not None and hasattr(fp, "build_records"):
+        return fp.build_records(nodes if isinstance(nodes, list) else list(nodes), *_native_args(res))
     gpu_nodes: List[Dict] = []
     ready_nodes: List[Dict] = []
     for pos, i in enumerate(res.gpu_idx.tolist()):
@@ -57,10 +70,25 @@ def build_records(nodes: Sequence[Any], res: engine.FleetResult) -> Tuple[List[D
     return gpu_nodes, ready_nodes
 
 
-def classify_nodes(nodes: Optional[Sequence[Any]], clf: Optional[engine.Classifier] = None):
+def classify_for_summary(nodes: Optional[Sequence[Any]], clf: Optional[engine.Classifier] = None):
+    """(nodes as a list, FleetResult): what `summary_json_from_result` and `build_records` take."""
     nodes = list(nodes or [])
-    res = classify_packed(pnl.pack_nodes(nodes), clf)
-    return build_records(nodes, res)
+    return nodes, classify_packed(pnl.pack_nodes(nodes), clf)
+
+
+class LastCall:
+    """What the most recent `list_gpu_nodes` classified: lets the CLI wrapper write the `--json` document
+    natively from the device's decisions instead of walking the list of dicts again (cli.py)."""
+    nodes: Optional[List[Any]] = None
+    result: Optional[engine.FleetResult] = None
+    gpu_nodes: Optional[List[Dict]] = None
+
+
+def classify_nodes(nodes: Optional[Sequence[Any]], clf: Optional[engine.Classifier] = None):
+    nodes, res = classify_for_summary(nodes, clf)
+    out = build_records(nodes, res)
+    LastCall.nodes, LastCall.result, LastCall.gpu_nodes = nodes, res, out[0]
+    return out
 
 
 def list_gpu_nodes(api, clf: Optional[engine.Classifier] = None) -> Tuple[List[Dict], List[Dict]]:
@@ -80,11 +108,7 @@ def summary_json_from_result(nodes: Sequence[Any], res: engine.FleetResult) -> s
     the extension is not built or a payload value has a type it does not format."""
     fp = pnl._fastpack()
     if fp is not None:
-        wide = {n: (sum(bd.values()), bd) for n, bd in res.wide.items()} if res.wide else None
-        totals = np.array([t if -2 ** 63 <= t < 2 ** 63 else 0 for t in res.gpu_total], dtype=np.int64) \
-            if res.wide else np.asarray(res.gpu_total, dtype=np.int64)
-        txt = fp.emit_summary_json(nodes, np.ascontiguousarray(res.gpu_idx, dtype=np.int64), np.ascontiguousarray(res.flags),
-                                   totals, np.ascontiguousarray(res.gpu_vals, dtype=np.int64).reshape(-1), wide, res.node_base)
+        txt = fp.emit_summary_json(nodes, *_native_args(res))
         if txt is not None:
             return txt
     g, r = build_records(nodes, res)

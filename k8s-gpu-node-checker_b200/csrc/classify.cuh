@@ -83,6 +83,7 @@ struct Params {
   const uint8_t* rows;
   const uint32_t* row_ptr;
   uint64_t rows_bytes;
+  uint32_t rows_lo;  // offsets below this are not readable (host-buffer path: `rows` is a staging buffer minus its first offset)
   uint32_t n_nodes;
   uint32_t node_base;
   uint32_t num_tiles;
@@ -689,7 +690,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         pl.hi = __ldg(p.row_ptr + first + pl.cnt);
         pl.lo_al = lo & ~15u;
         pl.bytes = ((pl.hi + 15u) & ~15u) - pl.lo_al;
-        pl.direct = pl.hi < lo || pl.hi > p.rows_bytes || pl.bytes > (uint32_t)STAGE_BYTES;
+        pl.direct = pl.hi < lo || pl.hi > p.rows_bytes || lo < p.rows_lo || pl.bytes > (uint32_t)STAGE_BYTES;
         if (!pl.direct && pl.bytes) bulk_prefetch_l2(p.rows + pl.lo_al, pl.bytes);
         bulk_prefetch_l2(p.row_ptr + first, ((pl.cnt + 1) * 4u + 15u) & ~15u);
       };
@@ -849,8 +850,8 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       if (live) {
         rs = sm.rp[s][j];
         re = sm.rp[s][j + 1];
-        bad_ptr = re < rs || re > sm.hi[s] || (!direct && rs < sm.rp[s][0]);
-        if (bad_ptr) rs = re = (direct ? 0u : sm.rp[s][0]);
+        bad_ptr = re < rs || re > sm.hi[s] || rs < (direct ? p.rows_lo : sm.rp[s][0]);
+        if (bad_ptr) rs = re = (direct ? p.rows_lo : sm.rp[s][0]);
       }
       NodeResult r;
       r.v01 = r.v23 = r.bits = 0;

@@ -607,7 +607,160 @@ done:
   return result;
 }
 
+
+/* ------------------------------------------------------------------------------------------------
+ * build_records: (gpu_nodes, ready_gpu_nodes) exactly as check-gpu-node.py:199-226 returns them -- one
+ * six-key dict per GPU node (name, ready, gpus, gpu_breakdown, labels, taints, in that order; :202-212),
+ * GPU nodes in fleet order, the Ready list holding the same dict objects (:222-225) -- from the device's
+ * decisions plus each node's pass-through payload, without a Python-level loop per node.
+ *   build_records(nodes, gpu_idx: int64 buffer[G], flags: uint8 buffer[N], totals: int64 buffer[G],
+ *                 vals: int64 buffer[G*4], wide: dict node -> (gpus:int, breakdown:dict) | None, node_base)
+ */
+static PyObject *s_ready, *s_gpus, *s_gpu_breakdown, *s_key_names[4];
+
+static PyObject* build_records(PyObject* self, PyObject* args) {
+  PyObject *nodes, *wide;
+  Py_buffer idx, flags, totals, vals;
+  long long node_base;
+  if (!PyArg_ParseTuple(args, "Oy*y*y*y*OL", &nodes, &idx, &flags, &totals, &vals, &wide, &node_base)) return NULL;
+  PyObject* seq = PySequence_Fast(nodes, "nodes must be a sequence");
+  PyObject *gpu_list = NULL, *ready_list = NULL, *result = NULL;
+  if (!seq) goto done;
+  {
+    const Py_ssize_t g = idx.len / 8, n_nodes = PySequence_Fast_GET_SIZE(seq);
+    const long long* gi = (const long long*)idx.buf;
+    const long long* gt = (const long long*)totals.buf;
+    const long long* gv = (const long long*)vals.buf;
+    const unsigned char* fl = (const unsigned char*)flags.buf;
+    const int have_wide = wide != Py_None && PyDict_Size(wide) > 0;
+    gpu_list = PyList_New(g);
+    ready_list = PyList_New(0);
+    if (!gpu_list || !ready_list) goto done;
+    for (Py_ssize_t i = 0; i < g; i++) {
+      const long long at = gi[i] - node_base;
+      if (at < 0 || at >= n_nodes || at >= flags.len) {
+        PyErr_SetString(PyExc_IndexError, "gpu_idx outside the node list");
+        goto done;
+      }
+      PyObject* node = PySequence_Fast_GET_ITEM(seq, at);
+      const unsigned f = fl[at];
+      PyObject *name = NULL, *labels = NULL, *taints = NULL, *gpus = NULL, *bd = NULL, *rec = NULL;
+      int ok = 0;
+      /* name / labels: check-gpu-node.py:203, :207 */
+      PyObject* md = PyObject_GetAttr(node, s_metadata);
+      if (!md) goto node_done;
+      {
+        const int md_true = PyObject_IsTrue(md);
+        if (md_true < 0) { Py_DECREF(md); goto node_done; }
+        if (md_true) {
+          name = PyObject_GetAttr(md, s_name);
+          labels = name ? PyObject_GetAttr(md, s_labels) : NULL;
+          if (labels) {
+            const int lt = PyObject_IsTrue(labels);
+            if (lt < 0) { Py_DECREF(md); goto node_done; }
+            if (!lt) { Py_DECREF(labels); labels = PyDict_New(); }
+          }
+        } else {
+          name = PyUnicode_FromString("");
+          labels = PyDict_New();
+        }
+        Py_DECREF(md);
+        if (!name || !labels) goto node_done;
+      }
+      /* taints: check-gpu-node.py:208-211 */
+      taints = PyList_New(0);
+      if (!taints) goto node_done;
+      {
+        PyObject* spec = PyObject_GetAttr(node, s_spec);
+        if (!spec) goto node_done;
+        const int st = PyObject_IsTrue(spec);
+        PyObject* src = NULL;
+        if (st > 0) {
+          src = PyObject_GetAttr(spec, s_taints);
+          if (!src) PyErr_Clear(); /* getattr(node.spec, "taints", None) */
+        }
+        Py_DECREF(spec);
+        if (st < 0) goto node_done;
+        if (src) {
+          const int tt = PyObject_IsTrue(src);
+          if (tt < 0) { Py_DECREF(src); goto node_done; }
+          if (tt) {
+            PyObject* it = PyObject_GetIter(src);
+            if (!it) { Py_DECREF(src); goto node_done; }
+            PyObject* t;
+            int bad = 0;
+            while (!bad && (t = PyIter_Next(it))) {
+              PyObject* k = PyObject_GetAttr(t, s_key);
+              PyObject* v = k ? PyObject_GetAttr(t, s_value) : NULL;
+              PyObject* e = v ? PyObject_GetAttr(t, s_effect) : NULL;
+              PyObject* d = e ? PyDict_New() : NULL;
+              bad = !d || PyDict_SetItem(d, s_key, k) || PyDict_SetItem(d, s_value, v) || PyDict_SetItem(d, s_effect, e) ||
+                    PyList_Append(taints, d);
+              Py_XDECREF(k); Py_XDECREF(v); Py_XDECREF(e); Py_XDECREF(d);
+              Py_DECREF(t);
+            }
+            Py_DECREF(it);
+            if (bad || PyErr_Occurred()) { Py_DECREF(src); goto node_done; }
+          }
+          Py_DECREF(src);
+        }
+      }
+      /* gpus / gpu_breakdown: from the device, or from the bignum table */
+      {
+        PyObject* wrec = NULL;
+        if (have_wide) {
+          PyObject* key = PyLong_FromLongLong(gi[i]);
+          wrec = key ? PyDict_GetItemWithError(wide, key) : NULL; /* borrowed */
+          Py_XDECREF(key);
+          if (!wrec && PyErr_Occurred()) goto node_done;
+        }
+        if (wrec) {
+          PyObject* gp = PyTuple_GetItem(wrec, 0);
+          PyObject* src = PyTuple_GetItem(wrec, 1);
+          if (!gp || !src) goto node_done;
+          gpus = gp;
+          Py_INCREF(gpus);
+          bd = PyDict_Copy(src);
+        } else {
+          gpus = PyLong_FromLongLong(gt[i]);
+          bd = PyDict_New();
+          for (int k = 0; k < 4 && bd; k++)
+            if (f & (8u << k)) {
+              PyObject* v = PyLong_FromLongLong(gv[4 * i + k]);
+              if (!v || PyDict_SetItem(bd, s_key_names[k], v)) { Py_XDECREF(v); Py_CLEAR(bd); break; }
+              Py_DECREF(v);
+            }
+        }
+        if (!gpus || !bd) goto node_done;
+      }
+      rec = PyDict_New();
+      if (!rec || PyDict_SetItem(rec, s_name, name) || PyDict_SetItem(rec, s_ready, (f & 2) ? Py_True : Py_False) ||
+          PyDict_SetItem(rec, s_gpus, gpus) || PyDict_SetItem(rec, s_gpu_breakdown, bd) || PyDict_SetItem(rec, s_labels, labels) ||
+          PyDict_SetItem(rec, s_taints, taints))
+        goto node_done;
+      if ((f & 2) && PyList_Append(ready_list, rec)) goto node_done;
+      PyList_SET_ITEM(gpu_list, i, rec); /* steals rec */
+      rec = NULL;
+      ok = 1;
+    node_done:
+      Py_XDECREF(name); Py_XDECREF(labels); Py_XDECREF(taints); Py_XDECREF(gpus); Py_XDECREF(bd); Py_XDECREF(rec);
+      if (!ok) goto done;
+    }
+    result = PyTuple_Pack(2, gpu_list, ready_list);
+  }
+done:
+  Py_XDECREF(gpu_list);
+  Py_XDECREF(ready_list);
+  Py_XDECREF(seq);
+  PyBuffer_Release(&idx);
+  PyBuffer_Release(&flags);
+  PyBuffer_Release(&totals);
+  PyBuffer_Release(&vals);
+  return result;
+}
+
 static PyMethodDef methods[] = {
+    {"build_records", build_records, METH_VARARGS, "(gpu_nodes, ready_gpu_nodes) as lists of dicts"},
     {"emit_summary_json", emit_summary_json, METH_VARARGS, "the --json document as text"},{"pack_nodes", pack_nodes, METH_VARARGS, "V1Node objects -> (rows bytes, row_ptr bytes, n)"},
                                 {NULL, NULL, 0, NULL}};
 static struct PyModuleDef moddef = {PyModuleDef_HEAD_INIT, "_fastpack", "PNL-v2 packer (C)", -1, methods};
@@ -626,5 +779,9 @@ PyMODINIT_FUNC PyInit__fastpack(void) {
   s_key = PyUnicode_InternFromString("key");
   s_value = PyUnicode_InternFromString("value");
   s_effect = PyUnicode_InternFromString("effect");
+  s_ready = PyUnicode_InternFromString("ready");
+  s_gpus = PyUnicode_InternFromString("gpus");
+  s_gpu_breakdown = PyUnicode_InternFromString("gpu_breakdown");
+  for (int k = 0; k < 4; k++) s_key_names[k] = PyUnicode_InternFromString(KEY_NAMES[k]);
   return PyModule_Create(&moddef);
 }

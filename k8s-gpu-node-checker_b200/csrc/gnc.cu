@@ -8,6 +8,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -364,7 +365,12 @@ int gnc_set_max_str_digits(gnc_ctx* c, int max_digits) {
   return GNC_OK;
 }
 
-int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* cuda_stream) {
+}  // extern "C"
+
+namespace {
+// gnc_classify with a lower bound for row offsets: the host-buffer path hands the kernel a staging
+// buffer minus the chunk's first offset, so offsets below `rows_lo` must be contained, not followed.
+int classify_impl(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* cuda_stream, uint32_t rows_lo) {
   if (!c) return GNC_ERR_ARG;
   int rc = check_batch(c, in, out);
   if (rc) return rc;
@@ -396,6 +402,7 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
   p.rows = in->rows;
   p.row_ptr = in->row_ptr;
   p.rows_bytes = in->rows_bytes;
+  p.rows_lo = rows_lo;
   p.n_nodes = in->n_nodes;
   p.node_base = in->node_base;
   p.num_tiles = tiles;
@@ -427,8 +434,20 @@ int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* c
   c->launches++;
   return GNC_OK;
 }
+}  // namespace
+
+extern "C" {
+
+int gnc_classify(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* cuda_stream) {
+  return classify_impl(c, in, out, cuda_stream, 0u);
+}
 
 uint64_t gnc_launch_count(const gnc_ctx* c) { return c ? c->launches : 0; }
+
+const char* gnc_variant_for(uint64_t rows_bytes, uint32_t n_nodes) {
+  gnc_ctx probe;  // forced_variant = -1: the choice made from the shard's shape alone
+  return kVariants[pick_variant(&probe, rows_bytes, n_nodes)].name;
+}
 
 int gnc_unicode_tables(const uint32_t** nd_runs, int* n_runs, const uint32_t** spaces, int* n_spaces) {
   static const uint32_t runs[GNC_ND_RUNS] = {GNC_ND_RUN_LIST};
@@ -514,7 +533,11 @@ extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_resu
     ~FleetPause() { c->fleet.on = was; }
   } fleet_pause(c);
   // Chunks of ~1M nodes: chunk k+1's upload overlaps chunk k's kernel and download.
-  const uint32_t kChunk = 1u << 20;
+  uint32_t kChunk = 1u << 20;
+  if (const char* e = getenv("GNC_HOST_CHUNK")) {  // tests: small chunks exercise the chunk seams
+    const long v = atol(e);
+    if (v >= 32 && v <= (1l << 24)) kChunk = (uint32_t)v;
+  }
   const uint32_t n = in->n_nodes;
   uint64_t g_total = 0, d_total = 0;
   int64_t acc[GNC_N_COUNTS] = {0};
@@ -545,7 +568,7 @@ extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_resu
     for (int s : {GNC_C_GPU_NODES, GNC_C_READY_NODES, GNC_C_DEFERRED, GNC_C_SCANNED, GNC_C_MALFORMED})
       acc[s] += h.h_counts[s];
     acc[GNC_C_OUT_DROPPED] += h.h_counts[GNC_C_OUT_DROPPED] + (int64_t)(g - gk);
-    acc[GNC_C_DEFER_DROPPED] += h.h_counts[GNC_C_DEFER_DROPPED] + (int64_t)((uint64_t)h.h_counts[GNC_C_DEFERRED] - dk);
+    acc[GNC_C_DEFER_DROPPED] += (int64_t)((uint64_t)h.h_counts[GNC_C_DEFERRED] - dk);  // the kernel's own drops are part of this difference
     for (int k = 0; k < 4; k++)
       key[k] += ((unsigned __int128)(uint64_t)h.h_counts[GNC_C_KEY_HI + k] << 64) | (uint64_t)h.h_counts[GNC_C_KEY_LO + k];
     g_total += gk;
@@ -553,15 +576,13 @@ extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_resu
     q.live = false;
     return GNC_OK;
   };
-  int b = 0;
-  const uint32_t defer_cap = out->defer ? std::max<uint32_t>(out->defer_cap, 1) : 1;
-  for (uint32_t first = 0; first < n; first += kChunk, b ^= 1) {
-    int rc = drain(b);
-    if (rc) return rc;
+  // One chunk: upload, classify, start the counts download.  Returns with the work enqueued.
+  auto submit = [&](int b, uint32_t first, uint32_t defer_cap) -> int {
     const uint32_t cnt = std::min(kChunk, n - first);
     const uint64_t b0 = in->row_ptr[first], b1 = in->row_ptr[first + cnt];
     if (b1 < b0 || b1 > in->rows_bytes) return fail(c, GNC_ERR_ARG, "row_ptr is not monotone inside rows_bytes");
     gnc_ctx::HostStage& h = c->hs[b];
+    int rc;
     if ((rc = ensure_host_stage(c, h, b1 - b0 + 16, cnt, defer_cap))) return rc;
     // rows are copied from a 16-byte aligned source offset so row_ptr can stay absolute minus a constant
     const uint64_t a0 = b0 & ~15ull;
@@ -569,8 +590,8 @@ extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_resu
     CUDA_TRY(c, cudaMemsetAsync(h.d_rows + (b1 - a0), 0, 48, h.stream));
     CUDA_TRY(c, cudaMemcpyAsync(h.d_row_ptr, in->row_ptr + first, (cnt + 1) * 4ull, cudaMemcpyHostToDevice, h.stream));
     gnc_batch db;
-    db.rows = h.d_rows - a0;  // device offsets == host offsets (never dereferenced below a0), so are defer offsets
-    db.row_ptr = h.d_row_ptr;
+    db.rows = h.d_rows - a0;  // device offsets == host offsets, so are defer offsets; the kernel treats any
+    db.row_ptr = h.d_row_ptr; // offset below a0 (a corrupt row_ptr inside the chunk) as a malformed row
     db.rows_bytes = b1;
     db.n_nodes = cnt;
     db.node_base = in->node_base + first;
@@ -587,17 +608,35 @@ extern "C" int gnc_classify_host(gnc_ctx* c, const gnc_batch* in, const gnc_resu
     CUDA_TRY(c, cudaMemsetAsync(h.d_row_ptr + cnt + 1, 0xFF, 7 * 4, h.stream));
     // both stages' kernels share the context's scratch: this one starts after the other stage's has ended
     if (c->hs[b ^ 1].kernel && pend[b ^ 1].live) CUDA_TRY(c, cudaStreamWaitEvent(h.stream, c->hs[b ^ 1].kernel, 0));
-    if ((rc = gnc_classify(c, &db, &dr, h.stream))) return rc;
+    if ((rc = classify_impl(c, &db, &dr, h.stream, (uint32_t)a0))) return rc;
     CUDA_TRY(c, cudaEventRecord(h.kernel, h.stream));
     CUDA_TRY(c, cudaMemcpyAsync(h.h_counts, h.d_counts, GNC_N_COUNTS * sizeof(int64_t), cudaMemcpyDeviceToHost, h.stream));
     CUDA_TRY(c, cudaEventRecord(h.done, h.stream));
     pend[b].live = true;
     pend[b].first = first;
     pend[b].cnt = cnt;
+    return GNC_OK;
+  };
+  // An error mid-pipeline leaves the other stage in flight: wait for both before the staging buffers
+  // (owned by the context, reused by the next call) and the caller's host buffers are let go.
+  auto bail = [&](int rc) -> int {
+    const std::string keep = c->err;
+    for (auto& h : c->hs)
+      if (h.stream) cudaStreamSynchronize(h.stream);
+    pend[0].live = pend[1].live = false;
+    c->err = keep;
+    return rc;
+  };
+  int b = 0;
+  const uint32_t defer_cap = out->defer ? std::max<uint32_t>(out->defer_cap, 1) : 1;
+  for (uint32_t first = 0; first < n; first += kChunk, b ^= 1) {
+    int rc = drain(b);
+    if (!rc) rc = submit(b, first, defer_cap);
+    if (rc) return bail(rc);
   }
   for (int k = 0; k < 2; k++, b ^= 1) {
     int rc = drain(b);
-    if (rc) return rc;
+    if (rc) return bail(rc);
   }
   memcpy(out->counts, acc, sizeof(acc));
   for (int k = 0; k < 4; k++) {
@@ -699,7 +738,7 @@ int comm_init(gnc_ctx* c, const void* id, size_t id_len) {
   memcpy(nid.bytes, id, sizeof(nid));
   NCCL_TRY(c, n->CommInitRank(&c->comm, c->world, nid, c->rank));
   CUDA_TRY(c, cudaMalloc((void**)&c->d_all_counts, (size_t)c->world * GNC_N_COUNTS * sizeof(int64_t)));
-  CUDA_TRY(c, cudaMallocHost((void**)&c->h_all_counts, (size_t)c->world * GNC_N_COUNTS * sizeof(int64_t)));
+  CUDA_TRY(c, cudaMallocHost((void**)&c->h_all_counts, ((size_t)c->world * GNC_N_COUNTS + 1) * sizeof(int64_t)));
   return GNC_OK;
 }
 
@@ -798,39 +837,88 @@ extern "C" int gnc_fleet_enable(gnc_ctx* c, uint32_t fleet_nodes_cap, void* cuda
   f.slot_u32 = gnc::kFleetHeader + f.cap;
   f.region_bytes = ((size_t)c->world * f.slot_u32 * 4 + 255) & ~(size_t)255;
   f.bytes = 2 * f.region_bytes + 3 * (size_t)c->world * 8 + 256;
+  // Every step below is collective.  A rank on which something fails still takes part in the two
+  // all-gathers (the second carries a success flag from every rank), so no rank is left waiting in a
+  // collective for one that has already returned; the fused gather is enabled only if all succeeded.
   char* local = nullptr;
-  CUDA_TRY(c, cudaMalloc((void**)&local, f.bytes));
-  CUDA_TRY(c, cudaMemset(local, 0, f.bytes));
-  cudaIpcMemHandle_t mine;
-  CUDA_TRY(c, cudaIpcGetMemHandle(&mine, local));
-  // every rank's handle to every rank (through the communicator that already exists)
   char* d_handles = nullptr;
-  std::vector<cudaIpcMemHandle_t> all(c->world);
-  CUDA_TRY(c, cudaMalloc((void**)&d_handles, sizeof(mine) * c->world));
-  CUDA_TRY(c, cudaMemcpyAsync(d_handles + sizeof(mine) * c->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, stream));
-  NCCL_TRY(c, n->AllGather(d_handles + sizeof(mine) * c->rank, d_handles, sizeof(mine), kNcclUint8, c->comm, stream));
-  CUDA_TRY(c, cudaMemcpyAsync(all.data(), d_handles, sizeof(mine) * c->world, cudaMemcpyDeviceToHost, stream));
-  CUDA_TRY(c, cudaStreamSynchronize(stream));
-  for (int q = 0; q < c->world; q++) {
-    if (q == c->rank) {
-      f.base[q] = local;
-    } else {
-      void* ptr = nullptr;
-      cudaError_t e = cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess);
-      if (e != cudaSuccess) {
-        for (int k = 0; k < q; k++)
-          if (k != c->rank) cudaIpcCloseMemHandle(f.base[k]);
-        cudaFree(local);
-        cudaFree(d_handles);
-        return fail(c, GNC_ERR_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+  int opened[gnc::kFleetMaxWorld] = {};
+  auto undo = [&]() {
+    for (int q = 0; q < c->world; q++)
+      if (opened[q]) cudaIpcCloseMemHandle(f.base[q]);
+    for (int q = 0; q < c->world; q++) f.base[q] = nullptr;
+    if (local) cudaFree(local);
+    if (d_handles) cudaFree(d_handles);
+  };
+  // a record per rank: its IPC handle, then a 64-byte status block whose first byte says "failed"
+  constexpr size_t kRec = sizeof(cudaIpcMemHandle_t) + 64;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "record layout");
+  struct Rec {
+    cudaIpcMemHandle_t h;
+    unsigned char bad[64];
+  };
+  static_assert(sizeof(Rec) == kRec, "record layout");
+  Rec mine = {};
+  std::string why;
+  auto note = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && why.empty()) why = std::string(what) + ": " + cudaGetErrorString(e);
+    return e == cudaSuccess;
+  };
+  bool ok = note(cudaMalloc((void**)&local, f.bytes), "cudaMalloc(fleet buffer)") && note(cudaMemset(local, 0, f.bytes), "cudaMemset") &&
+            note(cudaIpcGetMemHandle(&mine.h, local), "cudaIpcGetMemHandle");
+  mine.bad[0] = ok ? 0 : 1;
+  std::vector<Rec> all(c->world);
+  if (cudaMalloc((void**)&d_handles, kRec * c->world) != cudaSuccess) {
+    // without this staging buffer the rank cannot even take part in the collective: nothing to do but fail here
+    undo();
+    return fail(c, GNC_ERR_NOMEM, "gnc_fleet_enable: cannot allocate the handle exchange buffer");
+  }
+  auto exchange = [&]() -> int {  // every rank's record to every rank (through the communicator that already exists)
+    CUDA_TRY(c, cudaMemcpyAsync(d_handles + kRec * c->rank, &mine, kRec, cudaMemcpyHostToDevice, stream));
+    NCCL_TRY(c, n->AllGather(d_handles + kRec * c->rank, d_handles, kRec, kNcclUint8, c->comm, stream));
+    CUDA_TRY(c, cudaMemcpyAsync(all.data(), d_handles, kRec * c->world, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(c, cudaStreamSynchronize(stream));
+    return GNC_OK;
+  };
+  int rc = exchange();
+  if (rc) {
+    undo();
+    return rc;
+  }
+  for (int q = 0; q < c->world; q++) ok = ok && !all[q].bad[0];
+  if (ok) {
+    for (int q = 0; q < c->world && ok; q++) {
+      if (q == c->rank) {
+        f.base[q] = local;
+      } else {
+        void* ptr = nullptr;
+        ok = note(cudaIpcOpenMemHandle(&ptr, all[q].h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+        if (ok) {
+          f.base[q] = (char*)ptr;
+          opened[q] = 1;
+        }
       }
-      f.base[q] = (char*)ptr;
     }
   }
-  // nobody writes into a peer before every peer has zeroed its buffer: one more trip round the ranks
-  NCCL_TRY(c, n->AllGather(d_handles + sizeof(mine) * c->rank, d_handles, sizeof(mine), kNcclUint8, c->comm, stream));
-  CUDA_TRY(c, cudaStreamSynchronize(stream));
+  // nobody writes into a peer before every peer has zeroed its buffer and mapped the others: one more
+  // trip round the ranks, carrying each rank's verdict
+  mine.bad[0] = ok ? 0 : 1;
+  rc = exchange();
+  if (rc) {
+    undo();
+    return rc;
+  }
+  int first_bad = -1;
+  for (int q = 0; q < c->world; q++)
+    if (all[q].bad[0] && first_bad < 0) first_bad = q;
+  if (first_bad >= 0) {
+    undo();
+    cudaGetLastError();
+    return fail(c, GNC_ERR_CUDA, "gnc_fleet_enable: peer mapping unavailable (first failing rank " + std::to_string(first_bad) + ")" +
+                                     (why.empty() ? "" : "; here: " + why));
+  }
   CUDA_TRY(c, cudaFree(d_handles));
+  d_handles = nullptr;
   f.unpack_done = (unsigned int*)(local + f.bytes - 256);
   f.epoch = 0;
   f.on = true;
@@ -896,25 +984,36 @@ extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result*
   // Records too: offsets are needed on the host, so this path synchronises the stream once.
   // 1. every rank's counts block to every rank; the sum (exact, 128-bit for the key totals) is the
   //    all-reduce of the counts, and the per-rank GPU-node counts give the gather offsets
-  NCCL_TRY(c, n->AllGather(local->counts, c->d_all_counts, GNC_N_COUNTS, kNcclInt64, c->comm, stream));
-  CUDA_TRY(c, cudaMemcpyAsync(c->h_all_counts, c->d_all_counts, (size_t)c->world * GNC_N_COUNTS * sizeof(int64_t),
+  //    (slot 15 of the block is spare: it carries each rank's out_cap, so that "too small" is decided from
+  //    numbers every rank has -- a rank that returned on its own would leave the others in the group below)
+  constexpr int kBlk = GNC_N_COUNTS;
+  int64_t* mine_blk = c->d_all_counts + (size_t)c->rank * kBlk;
+  CUDA_TRY(c, cudaMemcpyAsync(mine_blk, local->counts, (GNC_N_COUNTS - 1) * sizeof(int64_t), cudaMemcpyDeviceToDevice, stream));
+  c->h_all_counts[(size_t)c->world * kBlk] = (int64_t)all->out_cap;   // pinned staging word past the blocks
+  CUDA_TRY(c, cudaMemcpyAsync(mine_blk + (GNC_N_COUNTS - 1), c->h_all_counts + (size_t)c->world * kBlk, sizeof(int64_t),
+                              cudaMemcpyHostToDevice, stream));
+  NCCL_TRY(c, n->AllGather(mine_blk, c->d_all_counts, kBlk, kNcclInt64, c->comm, stream));
+  CUDA_TRY(c, cudaMemcpyAsync(c->h_all_counts, c->d_all_counts, (size_t)c->world * kBlk * sizeof(int64_t),
                               cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(c, cudaStreamSynchronize(stream));
   int64_t sum[GNC_N_COUNTS] = {0};
   unsigned __int128 key[4] = {0, 0, 0, 0};
   std::vector<uint64_t> off(c->world + 1, 0);
+  uint64_t min_cap = ~0ull;
   for (int r = 0; r < c->world; r++) {
-    const int64_t* cr = c->h_all_counts + (size_t)r * GNC_N_COUNTS;
-    for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] += cr[s];
+    const int64_t* cr = c->h_all_counts + (size_t)r * kBlk;
+    for (int s = 0; s < GNC_N_COUNTS - 1; s++) sum[s] += cr[s];
     for (int k = 0; k < 4; k++)
       key[k] += ((unsigned __int128)(uint64_t)cr[GNC_C_KEY_HI + k] << 64) | (uint64_t)cr[GNC_C_KEY_LO + k];
     off[r + 1] = off[r] + (uint64_t)cr[GNC_C_GPU_NODES];
+    min_cap = std::min<uint64_t>(min_cap, (uint64_t)cr[GNC_N_COUNTS - 1]);
   }
   for (int k = 0; k < 4; k++) {
     sum[GNC_C_KEY_LO + k] = (int64_t)(uint64_t)key[k];
     sum[GNC_C_KEY_HI + k] = (int64_t)(uint64_t)(key[k] >> 64);
   }
-  if (off[c->world] > all->out_cap) return fail(c, GNC_ERR_OVERFLOW, "all.out_cap is smaller than the fleet's GPU-node count");
+  if (off[c->world] > min_cap)   // the same verdict on every rank
+    return fail(c, GNC_ERR_OVERFLOW, "some rank's all.out_cap is smaller than the fleet's GPU-node count");
   memcpy(c->h_all_counts, sum, sizeof(sum));  // reuse the pinned block as the upload source
   CUDA_TRY(c, cudaMemcpyAsync(all->counts, c->h_all_counts, sizeof(sum), cudaMemcpyHostToDevice, stream));
   // 2. all-gather-v of the compacted records: one broadcast per rank into its rank-ordered slice
@@ -961,6 +1060,9 @@ struct StaticState {
   int ctas_per_sm[kNumVariants];
 };
 StaticState g_static_state[kStaticMaxDevices];
+// Host threads that call in for the same or different devices take turns through the set-up, the epoch
+// bump and the launch; this orders the HOST side only -- kernels on different streams still share the array.
+std::mutex g_static_mutex;
 
 int static_fail(char* err, size_t cap, int code, const char* what, const char* detail) {
   if (err && cap) snprintf(err, cap, "%s%s%s", what, detail ? ": " : "", detail ? detail : "");
@@ -981,11 +1083,15 @@ extern "C" int gnc_classify_static(int device, const gnc_batch* in, const gnc_re
   if (!in || !out || !out->counts) return static_fail(err, err_cap, GNC_ERR_ARG, "null batch, result or counts", nullptr);
   if (max_str_digits < 0) return static_fail(err, err_cap, GNC_ERR_ARG, "max_str_digits is negative", nullptr);
   cudaStream_t stream = (cudaStream_t)cuda_stream;
+  std::lock_guard<std::mutex> guard(g_static_mutex);
   STATIC_CUDA_TRY(cudaSetDevice(device));
   StaticState& st = g_static_state[device];
   if (!st.ready) {
     // First call on this device (it is current): learn the device address of the scratch array and
-    // the launch geometry.  Nothing here allocates; it must not run inside a stream capture.
+    // the launch geometry.  No cudaMalloc here either, but this is where the CUDA runtime may create
+    // the device context and load this library's module -- which is when the scratch array and the
+    // kernel images take up their device memory -- so it can fail on a device whose memory is already
+    // full, and it must not run inside a stream capture.
     void* ptr = nullptr;
     STATIC_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
     cudaDeviceProp prop;

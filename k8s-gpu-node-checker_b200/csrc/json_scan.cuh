@@ -849,16 +849,23 @@ __device__ void find_last_members2(Cur& c, const char* lit_a, int len_a, const c
   }
 }
 
-// value at the cursor as a capacity quantity: how many bytes the PNL value has
-//   string -> decoded text; number -> its token, or nothing when it is zero (a falsy value is
-//   skipped, check-gpu-node.py:188); true/false/null/containers -> nothing (int(str(.)) fails or falsy)
-__device__ bool number_is_zero(const uint8_t* p, unsigned long long b, unsigned long long e) {
+// value at the cursor as a capacity quantity: how many bytes the PNL value has.  The client declares
+// status.capacity as dict(str, str) and converts every non-null value with str(.) (ApiClient.__deserialize
+// -> __deserialize_primitive: klass(data)); the reference then skips falsy strings and takes int(str(.))
+// (check-gpu-node.py:188, :192).  So:
+//   string -> decoded text;
+//   integer token -> itself, except that a zero ("0", "-0": json.loads gives int 0, str gives "0") is the
+//     one byte "0" -- truthy, kept, value 0, exactly like the string "0";
+//   a token with a fraction or an exponent -> a float, whose str() never passes int(): nothing;
+//   true / false ("True" / "False"), null (None: falsy), containers (their repr) -> nothing.
+__device__ int number_class(const uint8_t* p, unsigned long long b, unsigned long long e) {  // 0 float, 1 integer zero, 2 other integer
+  bool zero = true;
   for (unsigned long long i = b; i < e; i++) {
     const int ch = p[i];
-    if (ch == 'e' || ch == 'E') break;
-    if (ch >= '1' && ch <= '9') return false;
+    if (ch == '.' || ch == 'e' || ch == 'E') return 0;
+    if (ch >= '1' && ch <= '9') zero = false;
   }
-  return true;
+  return zero ? 1 : 2;
 }
 __device__ unsigned long long quantity_len(Cur c) {
   const int ch = c.peek();
@@ -866,7 +873,8 @@ __device__ unsigned long long quantity_len(Cur c) {
   if (ch == '-' || (ch >= '0' && ch <= '9')) {
     const unsigned long long b = c.i;
     skip_value(c);
-    return number_is_zero(c.p, b, c.i) ? 0 : c.i - b;
+    const int k = number_class(c.p, b, c.i);
+    return k == 0 ? 0 : k == 1 ? 1 : c.i - b;
   }
   return 0;
 }
@@ -877,9 +885,24 @@ __device__ void quantity_copy(Cur c, uint8_t* dst) {
   } else if (ch == '-' || (ch >= '0' && ch <= '9')) {
     const unsigned long long b = c.i;
     skip_value(c);
-    if (!number_is_zero(c.p, b, c.i))
+    const int k = number_class(c.p, b, c.i);
+    if (k == 1) *dst = '0';
+    else if (k == 2)
       for (unsigned long long i = b; i < c.i; i++) *dst++ = c.p[i];
   }
+}
+// a condition's type / status: declared 'str' in V1NodeCondition, so the client applies str(.) as well:
+// true -> "True" (a JSON true in `status` therefore counts as Ready), false -> "False"; numbers and
+// containers become texts that can equal neither "Ready" nor "True" and are stored empty; null stays None.
+__device__ unsigned long long cond_text_len(Cur c) {
+  const int ch = c.peek();
+  return ch == '"' ? string_len(c) : ch == 't' ? 4 : ch == 'f' ? 5 : 0;
+}
+__device__ void cond_text_copy(Cur c, uint8_t* dst) {
+  const int ch = c.peek();
+  if (ch == '"') string_copy(c, dst);
+  else if (ch == 't') memcpy(dst, "True", 4);
+  else if (ch == 'f') memcpy(dst, "False", 5);
 }
 
 // Row builder: pass 0 measures (entry counts, text bytes, widest length), pass 1 writes.
@@ -955,11 +978,11 @@ __device__ void emit_conditions(Cur c, RowOut& o) {  // cursor at '[' of the con
     unsigned long long tl = 0, sl = 0;
     if (tpos != ~0ull) {
       t.i = tpos;
-      if (t.peek() == '"') tl = string_len(t);
+      tl = cond_text_len(t);
     }
     if (spos != ~0ull) {
       s.i = spos;
-      if (s.peek() == '"') sl = string_len(s);
+      sl = cond_text_len(s);
     }
     if (!o.write) {
       o.n_cond++;
@@ -967,8 +990,8 @@ __device__ void emit_conditions(Cur c, RowOut& o) {  // cursor at '[' of the con
       o.maxlen = max(o.maxlen, max(tl, sl));
     } else {
       o.table(tl, sl);
-      if (tl) string_copy(t, o.row + o.text_off);
-      if (sl) string_copy(s, o.row + o.text_off + tl);
+      if (tl) cond_text_copy(t, o.row + o.text_off);
+      if (sl) cond_text_copy(s, o.row + o.text_off + tl);
       o.text_off += tl + sl;
     }
   }

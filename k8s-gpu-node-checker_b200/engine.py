@@ -109,6 +109,11 @@ class FleetResult:
         return {k: int(self.gpu_vals[pos, j]) for j, k in enumerate(KEYS) if f & (F_KEY0 << j)}
 
 
+def variant_for(rows_bytes: int, n_nodes: int) -> str:
+    """Name of the kernel variant gnc_classify picks for a shard of this shape (GNC_VARIANT unset)."""
+    return native.lib().gnc_variant_for(int(rows_bytes), int(n_nodes)).decode()
+
+
 def key_total(counts: np.ndarray, k: int) -> int:
     return (int(counts[C_KEY_HI + k]) << 64) + (int(counts[C_KEY_LO + k]) & ((1 << 64) - 1))
 
@@ -206,6 +211,15 @@ class Classifier:
                      16: "too many root-level arrays"}
             raise native.GncError(-1, "gnc_json_to_pnl: " + ", ".join(v for k, v in names.items() if status & k))
         return DeviceBatch(rows, row_ptr, int(h[0]), int(h[1])), h
+
+    def json_to_pnl_into(self, doc: torch.Tensor, nodes_cap: int, rows: torch.Tensor, row_ptr: torch.Tensor,
+                         info: torch.Tensor, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """The same scan into caller-held buffers, enqueued without waiting (gnc_json_to_pnl as it is):
+        `rows` uint8[rows_cap], `row_ptr` int32[nodes_cap + 8], `info` int64[8] -- read info[0..2] after a sync."""
+        s = stream or torch.cuda.current_stream(self.device)
+        out = native.JsonOut(rows.data_ptr(), row_ptr.data_ptr(), info.data_ptr(), rows.numel(), nodes_cap)
+        self._check(self.lib.gnc_json_to_pnl(self._h, ctypes.c_void_p(doc.data_ptr()), doc.numel(), ctypes.byref(out),
+                                             ctypes.c_void_p(s.cuda_stream)))
 
     # ---- host-buffer path (what a binding without device memory of its own calls) ------------
     def classify_host(self, p: pnl.PackedNodeList, node_base: int = 0, defer_cap: int = 4096,

@@ -38,7 +38,7 @@ class JsonOut(ctypes.Structure):
 
 
 EXPORTS = ("gnc_abi_version", "gnc_create", "gnc_comm_id", "gnc_reserve", "gnc_set_max_str_digits", "gnc_classify",
-           "gnc_gather", "gnc_fleet_enable", "gnc_classify_host", "gnc_classify_static", "gnc_json_to_pnl", "gnc_launch_count", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
+           "gnc_gather", "gnc_fleet_enable", "gnc_classify_host", "gnc_classify_static", "gnc_json_to_pnl", "gnc_launch_count", "gnc_variant_for", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
 
 
 class GncError(RuntimeError):
@@ -96,6 +96,8 @@ def lib() -> ctypes.CDLL:
     L.gnc_json_to_pnl.restype = i32
     L.gnc_launch_count.argtypes = [vp]
     L.gnc_launch_count.restype = ctypes.c_uint64
+    L.gnc_variant_for.argtypes = [ctypes.c_uint64, u32]
+    L.gnc_variant_for.restype = ctypes.c_char_p
     L.gnc_unicode_tables.argtypes = [ctypes.POINTER(ctypes.POINTER(u32)), ctypes.POINTER(i32),
                                      ctypes.POINTER(ctypes.POINTER(u32)), ctypes.POINTER(i32)]
     L.gnc_last_error.argtypes = [vp]

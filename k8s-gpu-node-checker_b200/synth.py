@@ -245,6 +245,30 @@ def template_rows(templates: Sequence[Dict[str, Any]]) -> List[bytes]:
     return [pnl.node_row(build_node(t)) for t in templates]
 
 
+def spec_row(spec: Dict[str, Any]) -> bytes:
+    """PNL-v2 row of a node spec without building client objects (so callers that only need bytes --
+    the benchmark's GPU arm -- do not need a `kubernetes` package).  Same marshalling as
+    `pnl.node_row(build_node(spec))`: tests/test_oracle_pnl.py holds the two equal on every template."""
+    if spec.get("status", True) is False:
+        return pnl.EMPTY_ROW
+    cap = spec.get("capacity")
+    conds = spec.get("conditions")
+    pairs = None
+    if cap:                                                  # dict(cap): a repeated key keeps its first position, last value
+        d: Dict[Any, Any] = {}
+        for k, v in cap:
+            d[k] = v
+        pairs = list(d.items())
+    cl = None
+    if conds:                                                # "plain:" entries are not V1NodeCondition objects: left out
+        cl = [(t, st) for t, st in conds if not (isinstance(t, str) and t.startswith("plain:"))]
+    return pnl.encode_row(pairs, cl)
+
+
+def spec_rows(templates: Sequence[Dict[str, Any]]) -> List[bytes]:
+    return [spec_row(t) for t in templates]
+
+
 def expand(rows: Sequence[bytes], tid, device=None):
     """(rows u8[T+pad], row_ptr u32-as-int64... ) -> torch tensors (rows: uint8, row_ptr: int32 view of u32).
 

@@ -14,7 +14,9 @@ hold every restatement here (Python and C) to those vectors.
 import os
 import sys
 
-STUB_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "k8s_stub")
+# the stand-in lives with the tests (tests/k8s_stub): it is test scaffolding, and code outside oracle/ that needs
+# V1Node objects (bench.py's seam leg) can put it on sys.path without importing this package
+STUB_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "k8s_stub")
 
 
 def ensure_kubernetes_importable():

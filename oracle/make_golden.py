@@ -3,7 +3,7 @@
     python -m oracle.make_golden
 
 Imports /root/reference/check-gpu-node.py through oracle/reference_loader.py (stub `kubernetes`,
-see oracle/k8s_stub) and records what ITS functions and ITS main() produce:
+see tests/k8s_stub) and records what ITS functions and ITS main() produce:
 
   readme_fixture.json   README.md:93-121's 2-node fleet: `--json` text, table text, exit code
   quantity_kat.json     gpu_capacity() (check-gpu-node.py:181-196) on every QUANTITY_CASES value

@@ -49,3 +49,14 @@ def test_no_cpu_fallback_in_product():
                 txt = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", txt, re.M), f
                 assert "pnl_oracle" not in txt, f
+
+
+def test_traffic_capture_names_the_kernel_variant_the_bench_runs(lib):
+    """bench.py reports roofline.traffic from profiles/classify_traffic.json only when that capture is of the
+    kernel variant gnc_classify picks for the workload: here the file is held to the library's own choice."""
+    import json
+    with open(os.path.join(ROOT, "profiles", "classify_traffic.json")) as f:
+        t = json.load(f)
+    assert lib.gnc_variant_for(t["rows_bytes"], t["nodes"]).decode() == t["variant"]
+    assert t["kernel"] == "gnc::classify_kernel" and t["dram_bytes_read"] > t["rows_bytes"] * 0.9
+    assert lib.gnc_variant_for(10 ** 9, 10 ** 6).decode() == "t32"       # 1000-byte rows: the smallest tile

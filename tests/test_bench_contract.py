@@ -21,18 +21,28 @@ def _run(args, timeout):
 
 
 def test_reference_arm_line():
-    d = _run(["--impl", "reference", "--steps", "1", "--warmup", "0"], 600)
+    d = _run(["--impl", "reference", "--steps", "1", "--warmup", "1", "--nodes", "500000"], 600)
     assert BASE_KEYS <= set(d) and d["impl"] == "reference" and d["gpu_launches"] == 0
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["value"] > 1e4
+    from oracle.reference_loader import reference_available
+    assert d["cpu_baseline"]["kind"] == ("reference" if reference_available() else "port")
+    assert d["cpu_baseline"]["cores"] >= 1 and d["value"] > 1e4 and d["config"]["nodes"] == 500000
+    assert d["detail"]["gpu_nodes"] > 0.6 * 500000
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]
 
 
 @pytest.mark.gpu
 def test_b200_arm_line():
-    d = _run(["--nodes", "400000", "--steps", "4", "--warmup", "3", "--e2e-steps", "1", "--cpu-sample", "20000"], 900)
-    assert BASE_KEYS | {"roofline", "clocks"} <= set(d)
+    d = _run(["--nodes", "400000", "--steps", "4", "--warmup", "3", "--e2e-steps", "1", "--cpu-sample", "20000",
+              "--json-nodes", "30000", "--json-steps", "2", "--json-cpu-sample", "2000", "--seam-nodes", "5000"], 900)
+    assert BASE_KEYS | {"roofline", "clocks", "verified", "json", "e2e_seam"} <= set(d)
+    assert d["verified"]["indices"] and d["verified"]["counts"] and d["verified"]["per_rank_outputs"] and d["verified"]["ranks"] == 1
+    j = d["json"]
+    assert j["verified"] == {"counts": True, "indices": True} and j["general_parser_nodes"] == 0 and j["gpu_launches"] > 2
+    assert 0 < j["roofline"]["frac"] < 1.5 and j["e2e"]["h2d_bytes_per_step"] == j["config"]["json_bytes"] and j["cpu_baseline"]["value"] > 0
+    s = d["e2e_seam"]
+    assert s["verified"] and s["summary_json"]["identical"] and s["value"] > 0 and s["reference"]["value"] > 0
     assert d["metric"] == "node_records_per_sec" and d["gpu_launches"] == 4 and d["n_gpus"] == 1
     r = d["roofline"]
     assert r["bound"] == "hbm" and 0 < r["frac"] < 1.5 and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
     assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0 and d["e2e"]["value"] < d["value"]
-    assert d["cpu_baseline"]["cores"] == 1 and d["config"]["gpu_nodes"] > 0.6 * 400000
+    assert d["cpu_baseline"]["cores"] == 1 and d["detail"]["gpu_nodes"] > 0.6 * 400000

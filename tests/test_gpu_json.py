@@ -91,6 +91,11 @@ DOCS = [
     b'"conditions":[{"type":"R\\u0065ady","status":"Tru\\u0065"},{"status":"True"},{"type":"Ready"},[],7]}}]}',
     b' \n{ "items" :\t[ { "status" : { "conditions" : [ ] , "capacity" : { } } } , { "st\\u0061tus" : { "c\\u0061pacity" : '
     b'{ "nvidia.com/gpu" : " 8 " } } } ] } \n',
+    # non-string scalars go through the client's str(): a JSON true in `status` is "True" (Ready), the integer
+    # zero is "0" (kept in gpu_breakdown with value 0) on a node that is a GPU node through another key
+    b'{"items":[{"status":{"capacity":{"nvidia.com/gpu":"2"},"conditions":[{"type":"Ready","status":true}]}},'
+    b'{"status":{"capacity":{"nvidia.com/gpu":-0,"amd.com/gpu":1,"intel.com/gpu":0},"conditions":[{"type":"Ready","status":false},'
+    b'{"type":true,"status":"True"}]}},{"status":{"capacity":{"nvidia.com/gpu":0},"conditions":[{"status":true,"type":"Ready"}]}}]}',
 ]
 
 
@@ -103,8 +108,8 @@ def test_small_documents(clf, k):
     assert batch.n_nodes == len(nodes)
     if len(nodes):
         assert_same_outputs(got, ora, f"doc {k}")
-        if k != 7:      # doc 7 has true/containers as quantities: the device writes "" where the client writes "True"/"{...}";
-            #             neither survives int(), the classification above is identical, only the unused text differs
+        if k != 7:      # doc 7 has floats/true/containers as quantities: the device writes "" where the client writes "-0.0"/"True"/"{...}";
+            #             none survives int(), the classification above is identical, only the unused text differs
             assert batch.rows.cpu().numpy()[:p.n_bytes].tobytes() == p.rows[:p.n_bytes].tobytes()
     else:
         assert not got["counts"].any()

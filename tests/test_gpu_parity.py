@@ -179,6 +179,60 @@ def test_host_buffer_entry_point(clf, g2):
     assert sorted(out["defer"]["node"][:d].tolist()) == exp["deferred_nodes"].tolist()
 
 
+def test_host_path_contains_corrupt_row_ptr_in_later_chunks(g2, monkeypatch):
+    """gnc_classify_host hands the kernel a staging buffer minus the chunk's first offset: a row_ptr entry
+    that points below the chunk (or past the data) must give malformed rows, not a read outside the buffer.
+    Small chunks put the damage in a second and third chunk, at a tile's first row (the tile is then read
+    directly from global memory) and in the middle of a staged tile."""
+    tmpl, rows, truth, _ = g2
+    monkeypatch.setenv("GNC_HOST_CHUNK", "1000")
+    n = 5000
+    _, tid = synth.fleet("g1", 5, 0, n)
+    p = pnl.from_rows([rows[t] for t in tid])
+    exp = expected_outputs(truth, tid)
+    c = engine.Classifier(0)
+    try:
+        clean = c.classify_host(p)
+        assert_same_outputs(clean, exp, "host path, small chunks")
+        rp = p.row_ptr.copy()
+        hit = [1000 + 224, 2500, 2600, 3000 + 448 + 17]          # tile starts of chunk 1 and 3, mid-tile in chunk 2
+        rp[hit[0]] = 16
+        rp[hit[1]] = 0
+        rp[hit[2]] = 0xFFFFFF00
+        rp[hit[3]] = rp[3000] - 4 if rp[3000] >= 4 else 0         # just below the chunk's first byte
+        out = c.classify_host(pnl.PackedNodeList(p.rows, rp, n))
+        touched = np.zeros(n, bool)
+        for h in hit:
+            touched[h - 1:h + 1] = True
+        np.testing.assert_array_equal(out["flags"][:n][~touched], exp["flags"][~touched])
+        assert all(out["flags"][h - 1] & F_MALFORMED for h in hit)           # the row that now ends before it starts / past the data
+        assert int(out["counts"][12]) >= len(hit) and int(out["counts"][3]) == n
+        again = c.classify_host(p)                                         # the context is still usable: nothing faulted
+        assert_same_outputs(again, exp, "host path after corrupt input")
+    finally:
+        c.close()
+
+
+def test_host_path_reports_deferred_drops_once(g2):
+    """defer_cap too small on the host path: counts[13] is the number of deferred nodes left out, once."""
+    tmpl, rows, truth, _ = g2
+    _, tid = synth.fleet("g2", 2, 0, 50000)
+    p = pnl.from_rows([rows[t] for t in tid])
+    exp = expected_outputs(truth, tid)
+    d = int(exp["counts"][2])
+    assert d > 40
+    c = engine.Classifier(0)
+    try:
+        with pytest.raises(native.GncError):
+            c.classify_host(p, defer_cap=d - 25)
+        out = engine.host_buffers(p.n_nodes, d - 25)
+        with pytest.raises(native.GncError):
+            c.classify_host(p, defer_cap=d - 25, out=out)
+        assert int(out["counts"][13]) == 25 and int(out["counts"][2]) == d
+    finally:
+        c.close()
+
+
 def test_malformed_rows_match_oracle(clf):
     from tests.test_oracle_pnl import bad_rows
     good, bad = bad_rows()

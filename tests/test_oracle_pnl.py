@@ -67,6 +67,14 @@ def test_fleet_counts_match_reference_main(g2, golden, kind, seed, n):
     assert int(got["counts"][1]) + extra_r == rec["ready_nodes"]
 
 
+def test_spec_rows_equal_packed_objects():
+    """synth.spec_row (no client objects) == the packer on the built V1Node, for every template."""
+    t = synth.g2_templates()
+    assert synth.spec_rows(t) == synth.template_rows(t)
+    dup = {"capacity": [["nvidia.com/gpu", "1"], ["cpu", "4"], ["nvidia.com/gpu", "8"]], "conditions": [["plain:Ready", "True"]]}
+    assert synth.spec_row(dup) == pnl.node_row(synth.build_node(dup))
+
+
 def test_expand_equals_row_concatenation(g2):
     """synth.expand (torch gather) builds the same bytes as joining packed rows."""
     tmpl, rows, _ = g2

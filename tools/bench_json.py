@@ -10,9 +10,6 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oracle import ensure_kubernetes_importable  # noqa: E402
-
-ensure_kubernetes_importable()
 from k8s_gpu_node_checker_b200 import engine, synth  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000

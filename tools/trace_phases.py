@@ -11,15 +11,12 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oracle import ensure_kubernetes_importable  # noqa: E402
-
-ensure_kubernetes_importable()
 from k8s_gpu_node_checker_b200 import native, engine, synth  # noqa: E402
 
 native.LIB_PATH = os.path.join(native.CSRC, "libgnc_trace.so")
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_000_000
 tmpl = synth.g1_templates()
-rows_t = synth.template_rows(tmpl)
+rows_t = synth.spec_rows(tmpl)
 tid = synth.g1_tid(0, 0, n)
 rows, rp, total = synth.expand(rows_t, torch.from_numpy(tid).cuda())
 clf = engine.Classifier(0)
