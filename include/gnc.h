@@ -138,7 +138,7 @@ int gnc_classify_host(gnc_ctx*, const gnc_batch* host_in, const gnc_result* host
  * cannot take the device-wide synchronisation and possible failure of an allocation on their path.)
  * The kernel's scratch is a fixed array inside libgnc.so, GNC_STATIC_SCRATCH_BYTES of device memory
  * that every GPU which loads the library holds until the process exits.  It serves shards of up to
- * GNC_STATIC_MAX_TILES tiles -- about 14.6M nodes of ordinary size (224 per tile), fewer when rows
+ * GNC_STATIC_MAX_TILES tiles -- about 16.7M nodes of ordinary size (256 per tile), fewer when rows
  * are large (down to 32 per tile, 2M nodes); a larger shard is refused with GNC_ERR_ARG and a text
  * saying so.  Inputs and outputs are the caller's DEVICE buffers, exactly as for gnc_classify;
  * max_str_digits is sys.get_int_max_str_digits() (4300 by default, 0 = no limit).

@@ -24,11 +24,17 @@ from typing import List, Optional
 
 
 def load_reference(path: str):
-    spec = importlib.util.spec_from_file_location("check_gpu_node_reference", path)
-    if spec is None or spec.loader is None:
+    """The reference script as a module: its source, or a byte-compiled copy of it (.pyc content under any name)."""
+    import importlib.machinery
+    if not os.path.isfile(path):
         raise FileNotFoundError(path)
+    with open(path, "rb") as f:
+        compiled = f.read(4) == importlib.util.MAGIC_NUMBER
+    loader = (importlib.machinery.SourcelessFileLoader if compiled else importlib.machinery.SourceFileLoader)(
+        "check_gpu_node_reference", path)
+    spec = importlib.util.spec_from_loader("check_gpu_node_reference", loader)
     mod = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(mod)
+    loader.exec_module(mod)
     return mod
 
 

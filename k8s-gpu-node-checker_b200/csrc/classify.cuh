@@ -6,7 +6,7 @@
 //             (cp.async.bulk + mbarrier complete_tx);
 //   walkers   one thread per node: scan the row's length table without a branch per entry, look at
 //             the text of the few candidate entries, publish flags / ranks / partial counts, and
-//             write the tile's GPU-node records kRing-1 iterations later from a private stash;
+//             write the tile's GPU-node records a few iterations later from a private stash;
 //   scan      two warps turn per-warp counts into output positions with a 512-tile-wide decoupled
 //             look-back over global descriptors and fold the tile's counts into registers.
 // GPU nodes come out in fleet order (ballot ranks + prefix, no atomics decide positions).  With the
@@ -31,8 +31,17 @@ __device__ __forceinline__ unsigned long long gtimer() {
   return t;
 }
 #define GNC_T(slot, it_, val) do { if (p.trace && (it_) < 64) p.trace[((size_t)blockIdx.x * 64 + (it_)) * 8 + (slot)] = (val); } while (0)
+// position markers for debugging a hang or fault: one word per warp in a (host-mapped) buffer past the timestamps
+#define GNC_D(code) do { if (p.trace && (threadIdx.x & 31) == 0) ((volatile unsigned long long*)p.trace)[160000 + blockIdx.x * 32 + (threadIdx.x >> 5)] = (unsigned long long)(code); } while (0)
 #else
 #define GNC_T(slot, it_, val) do { } while (0)
+#define GNC_D(code) do { } while (0)
+#endif
+#ifdef GNC_TRACE
+// per-tile progress: 1 ticket taken, 2 load issued, 3 walkers have it, 4 aggregate published (debugging)
+#define GNC_TILE(tile_, st_) do { if (p.trace && (uint32_t)(tile_) < 60000u) ((volatile unsigned long long*)p.trace)[200000 + (tile_)] = ((unsigned long long)blockIdx.x << 32) | ((unsigned long long)(threadIdx.x >> 5) << 8) | (st_); } while (0)
+#else
+#define GNC_TILE(tile_, st_) do { } while (0)
 #endif
 
 // ------------------------------------------------------------------------------------------------
@@ -587,6 +596,12 @@ __device__ __forceinline__ uint32_t lookback(const Params& p, int t, uint32_t to
       const uint32_t m = __ballot_sync(0xFFFFFFFFu, has_inc);
       top = m ? 31 - __clz(m) : -1;
       good = lane > top ? ok : true;
+#ifdef GNC_TRACE
+      {
+        const uint32_t badm = __ballot_sync(0xFFFFFFFFu, !good);
+        if (badm) GNC_D(0x5000000ull | ((unsigned long long)(uint32_t)(g0 + kLookbackSpan * (__ffs(badm) - 1)) << 32) | (uint32_t)(t & 0xFFFFF));
+      }
+#endif
     } while (!__all_sync(0xFFFFFFFFu, good));
     excl += __reduce_add_sync(0xFFFFFFFFu, lane > top ? sum : (lane == top ? incv : 0u));
     if (top >= 0) break;
@@ -599,14 +614,24 @@ __device__ __forceinline__ uint32_t lookback(const Params& p, int t, uint32_t to
 // ------------------------------------------------------------------------------------------------
 // The kernel.  TN nodes per tile, one thread per node.  Warps: TN/32 walkers, 1 producer, 2 scan.
 // ------------------------------------------------------------------------------------------------
-constexpr int kRing = 6;  // a tile's records are written kRing-1 iterations after it was walked
+// Walker groups.  A CTA's walkers form GROUPS groups of TN threads; the CTA's q-th tile is walked by group
+// q % GROUPS out of stage q % STAGES, so a CTA has GROUPS tiles being walked and STAGES - GROUPS being
+// loaded.  (What bounds the kernel is how many walker warps an SM holds -- they run dependent integer
+// chains, ~6 cycles per instruction -- and what bounds that is shared memory: with one group a CTA needs
+// two whole stages per TN walkers, with two groups three stages serve 2 TN walkers.)
+// Ring: a tile's records are written when its group is about to reuse the tile's ring slot, i.e.
+// kRing / GROUPS - 1 of the group's iterations after it was walked.
+template <int GROUPS>
+__host__ __device__ constexpr int ring_slots() { return GROUPS == 1 ? 6 : 8; }
 enum { P_GPU = 0, P_READY, P_DEFERRED, P_MALFORMED, P_KEY0, P_N = 8 };
 
-template <int TN, int STAGES, int STAGE_BYTES>
+template <int TN, int STAGES, int STAGE_BYTES, int GROUPS = 1>
 struct Smem {
+  static constexpr int kRing = ring_slots<GROUPS>();
   alignas(128) uint8_t stage[STAGES][STAGE_BYTES + 32];
   alignas(16) uint32_t rp[STAGES][TN + 8];
-  alignas(8) uint64_t full[STAGES];  // producer/TMA -> walkers: the stage holds a tile
+  alignas(8) uint64_t full[STAGES][GROUPS];  // producer/TMA -> the group that walks the tile: the stage holds it.  One barrier per
+                                             // (stage, group): a waiter must see every phase of its barrier, or parities alias
   uint64_t pref_full[kRing];         // scan warp -> walkers: output positions are in warp_base[]
   unsigned long long acc[GNC_N_COUNTS];
   int tile[STAGES];
@@ -621,30 +646,34 @@ struct Smem {
   uint8_t stash_meta[kRing][TN];           // bit 0 GPU node, bit 1 wide, bits 2..6 rank in warp
 };
 
-template <int TN>
-__host__ __device__ constexpr int cta_threads() { return TN + 96; }
+template <int TN, int GROUPS = 1>
+__host__ __device__ constexpr int cta_threads() { return GROUPS * TN + 96; }
 
 // FLEET: the fused multi-GPU gather (peer stores while emitting); compiled out of the single-GPU kernels.
-template <int TN, int STAGES, int STAGE_BYTES, int MIN_CTAS, bool FLEET>
-__global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(const __grid_constant__ Params p) {
-  using S = Smem<TN, STAGES, STAGE_BYTES>;
+template <int TN, int STAGES, int STAGE_BYTES, int MIN_CTAS, bool FLEET, int GROUPS = 1>
+__global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_kernel(const __grid_constant__ Params p) {
+  using S = Smem<TN, STAGES, STAGE_BYTES, GROUPS>;
   extern __shared__ __align__(128) uint8_t smem_raw[];
   S& sm = *reinterpret_cast<S*>(smem_raw);
-  constexpr int kWalkWarps = TN / 32;
+  constexpr int kWalkWarps = TN / 32;            // per group
+  constexpr int kAllWalkWarps = GROUPS * kWalkWarps;
+  constexpr int kRing = S::kRing;
+  constexpr int kStagePeriod = (STAGES % GROUPS == 0) ? STAGES : STAGES * GROUPS;  // lcm, for 1 or 2 groups
   static_assert(TN % 32 == 0 && kWalkWarps <= 32 && TN < 1024, "one scan-warp lane per walker warp; 10-bit tile counts");
+  static_assert(GROUPS == 1 || GROUPS == 2, "two scan warps: they alternate (one group) or serve a group each");
+  static_assert(kRing % 2 == 0 && kRing % GROUPS == 0 && STAGES > GROUPS - 1 + 0, "ring slots and stages per group");
   // Hand-offs to warps that would otherwise do nothing but poll use hardware named barriers (the
   // waiting warp is descheduled, it issues nothing): stage s free -> producer, counts of ring slot b
   // ready -> the scan warp that owns slot b.  Both have TN walker threads arriving and one warp waiting.
-  static_assert(kRing % 2 == 0, "ring slot b always belongs to scan warp b & 1");
+  // (ring slot b always belongs to scan warp b & 1, and with two groups to group b & 1)
   constexpr int kBarStage = 1, kBarCnt = 1 + STAGES, kBarThreads = TN + 32;
   static_assert(kBarCnt + kRing <= 16, "named barrier ids");
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
-    for (int s = 0; s < STAGES; s++) {
-      mbar_init(&sm.full[s], 1);
-    }
+    for (int s = 0; s < STAGES; s++)
+      for (int g = 0; g < GROUPS; g++) mbar_init(&sm.full[s][g], 1);
     for (int b = 0; b < kRing; b++) {
       mbar_init(&sm.pref_full[b], 1);
     }
@@ -664,97 +693,115 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
   }
   __syncthreads();
 
-  if (warp == kWalkWarps) {
+  if (warp == kAllWalkWarps) {
     // ------------------------------ producer ------------------------------
     {
-      // Tickets are taken kAhead tiles before the tile is copied to shared memory (one is best: more lead
-      // puts ticket order further from completion order and the look-backs wait longer), and the tile's
-      // bytes are prefetched into L2 at once: HBM latency is then paid while the stage is still
-      // busy with an earlier tile, and the later bulk copy is an L2 hit.
-      constexpr int kAhead = 1, kQ = kAhead + 1;
+      // Lane 0 runs a small software pipeline, the other lanes only keep it company at the named barrier.  A
+      // tile costs two dependent trips to L2 before its bytes can be asked for -- the ticket (atomicAdd, tiles
+      // are handed out in fleet order), then the two row_ptr bounds -- ~1.4 us, which with one CTA per SM
+      // and two walker groups is most of a tile period.  So the trips of different tiles overlap: in the
+      // iteration that copies tile `it` to shared memory, the ticket of tile it + 2 and the bounds of tile
+      // it + 1 are requested first and used last.  Tile it + 1 is prefetched into L2 as soon as its bounds
+      // are known: HBM latency is then paid while its stage is still busy with an earlier tile, and the later
+      // bulk copy is an L2 hit.  (More lead than that puts ticket order further from completion order and the
+      // look-backs wait longer.)
       struct Plan {
         int tile;  // -1: no more tiles
         uint32_t lo_al, hi, bytes, cnt;
         bool direct;
-      } q[kQ];
-      auto plan = [&](Plan& pl) {
-        const uint32_t tile = atomicAdd(&p.scratch->ticket, 1u);
-        if (tile >= p.num_tiles) {
-          pl.tile = -1;
-          return;
-        }
+      };
+      auto finish_plan = [&](uint32_t tile, uint32_t lo, uint32_t hi) {
+        Plan pl;
         const uint32_t first = tile * TN;
         pl.tile = (int)tile;
         pl.cnt = min((uint32_t)TN, p.n_nodes - first);
-        const uint32_t lo = __ldg(p.row_ptr + first);
-        pl.hi = __ldg(p.row_ptr + first + pl.cnt);
+        pl.hi = hi;
         pl.lo_al = lo & ~15u;
         pl.bytes = ((pl.hi + 15u) & ~15u) - pl.lo_al;
         pl.direct = pl.hi < lo || pl.hi > p.rows_bytes || lo < p.rows_lo || pl.bytes > (uint32_t)STAGE_BYTES;
         if (!pl.direct && pl.bytes) bulk_prefetch_l2(p.rows + pl.lo_al, pl.bytes);
         bulk_prefetch_l2(p.row_ptr + first, ((pl.cnt + 1) * 4u + 15u) & ~15u);
+        return pl;
       };
-#pragma unroll
-      for (int k = 0; k < kQ; k++) q[k].tile = -1;
-      bool dry = false;
+      Plan cur;
+      cur.tile = -1;
+      int next_tile = -1;  // ticket of tile it + 1
+      bool dry = false;    // a ticket past the last tile has been drawn: no more are taken
       if (lane == 0) {
-#pragma unroll
-        for (int k = 0; k < kAhead; k++)
-          if (!dry) {
-            plan(q[k]);
-            dry = q[k].tile < 0;
-          }
+        const uint32_t t0 = atomicAdd(&p.scratch->ticket, 1u);
+        if (t0 < p.num_tiles) {
+          GNC_TILE(t0, 1);
+          const uint32_t t1 = atomicAdd(&p.scratch->ticket, 1u);
+          const uint32_t first = t0 * TN;
+          cur = finish_plan(t0, __ldg(p.row_ptr + first), __ldg(p.row_ptr + first + min((uint32_t)TN, p.n_nodes - first)));
+          if (t1 < p.num_tiles) next_tile = (int)t1;
+          else dry = true;
+        } else {
+          dry = true;
+        }
       }
-      // lane 0 does the work; the whole warp waits at the named barrier, so the loop is warp-uniform
+      int ended = 0;
       for (uint32_t it = 0;; ++it) {
         const int s = it % STAGES;
-        // the plan for tile it + kAhead goes into the slot freed by tile it - 1
-        Plan cur;
-        cur.tile = -1;
-        if (lane == 0) {
-#pragma unroll
-          for (int k = 0; k < kQ; k++) {
-            if ((int)(it % kQ) == k) cur = q[k];
-            if ((int)((it + kAhead) % kQ) == k) {
-              if (!dry) {
-                plan(q[k]);
-                dry = q[k].tile < 0;
-              } else {
-                q[k].tile = -1;
-              }
-            }
+        uint32_t ticket = 0, lo1 = 0, hi1 = 0;
+        if (lane == 0) {  // requested now, looked at after this tile's copy has been issued
+          if (!dry) ticket = atomicAdd(&p.scratch->ticket, 1u);
+          if (next_tile >= 0) {
+            const uint32_t first = (uint32_t)next_tile * TN;
+            lo1 = __ldg(p.row_ptr + first);
+            hi1 = __ldg(p.row_ptr + first + min((uint32_t)TN, p.n_nodes - first));
           }
         }
         const int cur_tile = __shfl_sync(0xFFFFFFFFu, cur.tile, 0);
+        GNC_D(0x1000000ull | (it << 8) | 1);
         if (it >= (uint32_t)STAGES) named_bar_sync(kBarStage + s, kBarThreads);  // every walker has left stage s
-        if (cur_tile < 0) {
+        GNC_D(0x1000000ull | (it << 8) | 2);
+        if (cur_tile < 0) {  // no more tiles: one end marker per group, in the stages their next tiles would have used
           if (lane == 0) {
             sm.tile[s] = -1;
-            mbar_arrive(&sm.full[s]);
+            mbar_arrive(&sm.full[s][it % GROUPS]);
           }
-          break;
+          if (++ended == GROUPS) break;
+          continue;
         }
-        if (lane != 0) continue;
-        const uint32_t first = (uint32_t)cur.tile * TN;
-        const uint32_t rp_bytes = ((cur.cnt + 1) * 4u + 15u) & ~15u;
-        sm.tile[s] = cur.tile;
-        sm.lo[s] = cur.lo_al;
-        sm.hi[s] = cur.direct ? (uint32_t)min(p.rows_bytes, (uint64_t)0xFFFFFFFFu) : cur.hi;
-        sm.direct[s] = cur.direct ? 1u : 0u;
-        const uint32_t stage_bytes = cur.direct ? 0u : cur.bytes;
-        mbar_arrive_expect_tx(&sm.full[s], rp_bytes + stage_bytes);
-        bulk_g2s(sm.rp[s], p.row_ptr + first, rp_bytes, &sm.full[s]);
-        if (stage_bytes) bulk_g2s(sm.stage[s], p.rows + cur.lo_al, stage_bytes, &sm.full[s]);
+        if (lane == 0) {
+          const uint32_t first = (uint32_t)cur.tile * TN;
+          const uint32_t rp_bytes = ((cur.cnt + 1) * 4u + 15u) & ~15u;
+          sm.tile[s] = cur.tile;
+          sm.lo[s] = cur.lo_al;
+          sm.hi[s] = cur.direct ? (uint32_t)min(p.rows_bytes, (uint64_t)0xFFFFFFFFu) : cur.hi;
+          sm.direct[s] = cur.direct ? 1u : 0u;
+          const uint32_t stage_bytes = cur.direct ? 0u : cur.bytes;
+          uint64_t* full = &sm.full[s][it % GROUPS];
+          mbar_arrive_expect_tx(full, rp_bytes + stage_bytes);
+          bulk_g2s(sm.rp[s], p.row_ptr + first, rp_bytes, full);
+          if (stage_bytes) bulk_g2s(sm.stage[s], p.rows + cur.lo_al, stage_bytes, full);
+          GNC_TILE(cur.tile, 2 | (it << 16));
+          // the next tile's plan (and its L2 prefetch), the ticket after that
+          cur.tile = -1;
+          if (next_tile >= 0) cur = finish_plan((uint32_t)next_tile, lo1, hi1);
+          next_tile = -1;
+          if (!dry) {
+            if (ticket < p.num_tiles) {
+              next_tile = (int)ticket;
+              GNC_TILE(ticket, 1);
+            } else {
+              dry = true;
+            }
+          }
+        }
       }
     }
     __syncwarp();  // lanes 1..31 rejoin lane 0 before the CTA-wide barrier below
-  } else if (warp > kWalkWarps) {
+  } else if (warp > kAllWalkWarps) {
     // ------------------------------ scan warps: this CTA's tile `it` goes to warp it & 1 -------------
     long long a_gpu = 0, a_ready = 0, a_def = 0, a_bad = 0, a_key[4] = {0, 0, 0, 0};  // lane 0 only
-    for (uint32_t it = warp - kWalkWarps - 1;; it += 2) {
+    for (uint32_t it = warp - kAllWalkWarps - 1;; it += 2) {
       const int b = it % kRing;
+      GNC_D(0x2000000ull | (it << 8) | 1);
       named_bar_sync(kBarCnt + b, kBarThreads);  // the walkers' partial counts of this tile are in part[b]
       const int tile = sm.scan_tile[b];
+      GNC_D(0x2000000ull | (it << 8) | 2 | ((unsigned long long)(uint32_t)tile << 32));
       if (tile < 0) break;
       GNC_T(5, it, gtimer());
       int part[P_N];
@@ -793,19 +840,23 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
     __syncwarp();
   } else {
     // ------------------------------ walkers: thread j owns node j of every tile -------------------
-    const int j = tid;
-    uint32_t lag_first[kRing - 1];  // first node of the tiles walked 1 .. kRing-1 iterations ago (registers: static indices only)
+    // (of the tiles its group walks: the CTA's tiles grp, grp + GROUPS, ...; `it` below is the CTA's tile number)
+    const int grp = warp / kWalkWarps, wg = warp - grp * kWalkWarps;
+    const int j = wg * 32 + lane;
+    constexpr int kLag = kRing / GROUPS - 1;  // a tile's records are written this many of the group's iterations after it was walked
+    uint32_t lag_first[kLag];  // first node of the tiles walked 1 .. kLag iterations ago (registers: static indices only)
 #pragma unroll
-    for (int q = 0; q < kRing - 1; q++) lag_first[q] = 0;
+    for (int q = 0; q < kLag; q++) lag_first[q] = 0;
 
     // Write a stashed tile's GPU-node records now that its output positions are known.
     auto emit_stashed = [&](uint32_t it_e, uint32_t first_e) {
       const int b = it_e % kRing;
       mbar_wait(&sm.pref_full[b], (it_e / kRing) & 1u);
+      GNC_D(0x3000000ull | (it_e << 8) | 7 | ((unsigned long long)sm.warp_base[b][wg] << 32));
       const uint32_t meta = sm.stash_meta[b][j];
       bool dropped = false;
       if (meta & 1u) {
-        const uint32_t pos = sm.warp_base[b][warp] + (meta >> 2);
+        const uint32_t pos = sm.warp_base[b][wg] + (meta >> 2);
         if (pos < p.out_cap) {
           long long v0, v1, v2, v3;
           if (meta & 2u) {  // values did not fit 16 bits: read them again from the row
@@ -831,13 +882,16 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       }
     };
 
-    uint32_t it = 0;
-    for (;; ++it) {
+    uint32_t it = grp;
+    for (;; it += GROUPS) {
       const int s = it % STAGES;
-      mbar_wait(&sm.full[s], (it / STAGES) & 1u);
+      GNC_D(0x3000000ull | (it << 8) | 1);
+      mbar_wait(&sm.full[s][grp], (it / kStagePeriod) & 1u);  // this group's tiles come to stage s every kStagePeriod tiles
       const int tile = sm.tile[s];
+      GNC_D(0x3000000ull | (it << 8) | 2 | ((unsigned long long)(uint32_t)tile << 32));
       if (tile < 0) break;
-      if (tid == 0) GNC_T(0, it, gtimer());
+      if (lane == 0 && wg == 0) GNC_TILE(tile, 3 | (it << 16));
+      if (tid == 0) GNC_T(0, it / GROUPS, gtimer());
       const uint32_t first = (uint32_t)tile * TN;
       const uint32_t cnt = min((uint32_t)TN, p.n_nodes - first);
       const bool live = (uint32_t)j < cnt;
@@ -853,6 +907,7 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         bad_ptr = re < rs || re > sm.hi[s] || rs < (direct ? p.rows_lo : sm.rp[s][0]);
         if (bad_ptr) rs = re = (direct ? p.rows_lo : sm.rp[s][0]);
       }
+      GNC_D(0x3000000ull | (it << 8) | 8 | ((unsigned long long)(rs - lo_al) << 32) | ((unsigned long long)direct << 63) | ((unsigned long long)bad_ptr << 62));
       NodeResult r;
       r.v01 = r.v23 = r.bits = 0;
       if (live) {
@@ -862,8 +917,9 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         }
       }
       __syncwarp();
+      GNC_D(0x3000000ull | (it << 8) | 3);
       named_bar_arrive(kBarStage + s, kBarThreads);  // this warp no longer reads the stage
-      if (tid == 0) GNC_T(1, it, gtimer());
+      if (tid == 0) GNC_T(1, it / GROUPS, gtimer());
 
       // -------- flags, ranks, partial counts; the records go out kRing-1 iterations later --------
       long long wv[4] = {0, 0, 0, 0};  // exact values of a wide node (rare)
@@ -895,12 +951,12 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
       const int s3 = __reduce_add_sync(0xFFFFFFFFu, count_narrow ? v3 : 0);
       const int b = it % kRing;
       if (lane == 0) {
-        int4* pp = reinterpret_cast<int4*>(sm.part[b][warp]);
+        int4* pp = reinterpret_cast<int4*>(sm.part[b][wg]);
         pp[0] = make_int4(__popc(gb), (int)n_ready, (int)n_def, (int)n_bad);  // P_GPU, P_READY, P_DEFERRED, P_MALFORMED
         pp[1] = make_int4(s0, s1, s2, s3);                                     // P_KEY0 ..
-        if (warp == 0) sm.scan_tile[b] = tile;
+        if (wg == 0) sm.scan_tile[b] = tile;
         if (FLEET && (uint32_t)(tile + 1) * (kWalkWarps + 1) <= p.fleet_cap) {
-          const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1) + 1 + warp;
+          const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1) + 1 + wg;
           for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][at] = gb;
         }
         // the last warp to count its share publishes the tile's aggregate at once: other CTAs'
@@ -909,9 +965,11 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         if ((old >> 16) == (uint32_t)kWalkWarps - 1) {
           sm.tile_cnt[b] = 0;
           st_volatile_u32(p.agg + tile, ((p.epoch & kEpochMask) << 10) | ((old & 0xFFFFu) + (uint32_t)__popc(gb)));
+          GNC_TILE(tile, 4 | (it << 16));
         }
       }
       __syncwarp();
+      GNC_D(0x3000000ull | (it << 8) | 4);
       named_bar_arrive(kBarCnt + b, kBarThreads);  // the scan warp can start on this tile
       if (is_gpu && wide) {
 #pragma unroll
@@ -922,32 +980,39 @@ __global__ void __launch_bounds__(cta_threads<TN>(), MIN_CTAS) classify_kernel(c
         if (slot < p.defer_cap) emit_defer(p, first + j, rs, re, slot);
         else atomicAdd(&sm.acc[GNC_C_DEFER_DROPPED], 1ull);
       }
-      if (tid == 0) GNC_T(2, it, gtimer());
+      if (tid == 0) GNC_T(2, it / GROUPS, gtimer());
 
-      // the tile walked kRing-1 iterations ago: its positions have had that long to arrive
-      if (it >= kRing - 1) emit_stashed(it - (kRing - 1), lag_first[kRing - 2]);
-      if (tid == 0) GNC_T(3, it, gtimer());
+      // the tile this group walked kLag iterations ago: its positions have had that long to arrive
+      GNC_D(0x3000000ull | (it << 8) | 5);
+      if (it >= (uint32_t)(kLag * GROUPS)) emit_stashed(it - kLag * GROUPS, lag_first[kLag - 1]);
+      GNC_D(0x3000000ull | (it << 8) | 6);
+      if (tid == 0) GNC_T(3, it / GROUPS, gtimer());
       sm.stash_vals[b][j] = make_uint2(r.v01, r.v23);
       sm.stash_meta[b][j] = (uint8_t)((is_gpu ? 1u : 0u) | (wide ? 2u : 0u) | (rank << 2));
 #pragma unroll
-      for (int q = kRing - 2; q > 0; q--) lag_first[q] = lag_first[q - 1];
+      for (int q = kLag - 1; q > 0; q--) lag_first[q] = lag_first[q - 1];
       lag_first[0] = first;
-      if (tid == 0) GNC_T(4, it, gtimer());
+      if (tid == 0) GNC_T(4, it / GROUPS, gtimer());
     }
     if (tid == 0) GNC_T(7, 1, gtimer());  // last tile walked
-    // drain the ring, then release both scan warps: their next phase completes with no tile
+    // drain the ring, then release the scan warps that wait for this group (both of them when there is one
+    // group, its own when there are two): their next phase completes with no tile
 #pragma unroll
-    for (int q = kRing - 2; q >= 0; q--)
-      if (it >= (uint32_t)q + 1) emit_stashed(it - (q + 1), lag_first[q]);
+    for (int q = kLag - 1; q >= 0; q--)
+      if (it >= (uint32_t)((q + 1) * GROUPS)) emit_stashed(it - (q + 1) * GROUPS, lag_first[q]);
     __syncwarp();
-    if (tid == 0) sm.scan_tile[it % kRing] = sm.scan_tile[(it + 1) % kRing] = -1;
-    __syncwarp();
-    named_bar_arrive(kBarCnt + (int)(it % kRing), kBarThreads);
-    named_bar_arrive(kBarCnt + (int)((it + 1) % kRing), kBarThreads);
+#pragma unroll
+    for (int d = 0; d < 2; d += GROUPS) {
+      if (j == 0) sm.scan_tile[(it + d) % kRing] = -1;
+      __syncwarp();
+      named_bar_arrive(kBarCnt + (int)((it + d) % kRing), kBarThreads);
+    }
   }
 
   // ------------------------------ grid-wide finish ------------------------------
+  GNC_D(0x4000000ull);
   __syncthreads();
+  GNC_D(0x4000001ull);
   if (tid == 0) GNC_T(7, 2, gtimer());  // ring drained, every warp here
   // One thread per count: done by thread 0 alone, the sixteen dependent round trips to L2 here and in the
   // last CTA below were ~10 us at the very end of every launch.

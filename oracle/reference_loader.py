@@ -30,8 +30,8 @@ def load_reference(path: str | None = None):
     ensure_kubernetes_importable()
     path = path or reference_path()
     if path is None:
-        raise FileNotFoundError("neither /root/reference/check-gpu-node.py nor oracle/_ref/check_gpu_node.pyc exists")
-    loader = (importlib.machinery.SourcelessFileLoader if path.endswith(".pyc") else importlib.machinery.SourceFileLoader)(
+        raise FileNotFoundError("neither /root/reference/check-gpu-node.py nor oracle/_ref/check_gpu_node.bin exists")
+    loader = (importlib.machinery.SourcelessFileLoader if path.endswith((".pyc", ".bin")) else importlib.machinery.SourceFileLoader)(
         "cgn_reference", path)
     spec = importlib.util.spec_from_loader("cgn_reference", loader)
     mod = importlib.util.module_from_spec(spec)

@@ -60,3 +60,4 @@ def test_traffic_capture_names_the_kernel_variant_the_bench_runs(lib):
     assert lib.gnc_variant_for(t["rows_bytes"], t["nodes"]).decode() == t["variant"]
     assert t["kernel"] == "gnc::classify_kernel" and t["dram_bytes_read"] > t["rows_bytes"] * 0.9
     assert lib.gnc_variant_for(10 ** 9, 10 ** 6).decode() == "t32"       # 1000-byte rows: the smallest tile
+    assert lib.gnc_variant_for(300 * 10 ** 6, 10 ** 6).decode() == "t192g2"

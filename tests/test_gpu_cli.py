@@ -13,7 +13,7 @@ from k8s_gpu_node_checker_b200 import api, cli, engine, pnl, synth
 from oracle.reference_loader import reference_path
 
 pytestmark = pytest.mark.gpu
-needs_ref = pytest.mark.skipif(reference_path() is None, reason="no reference script and no oracle/_ref/check_gpu_node.pyc on this machine")
+needs_ref = pytest.mark.skipif(reference_path() is None, reason="no reference script and no oracle/_ref/check_gpu_node.bin on this machine")
 
 
 def _run(argv, nodes):

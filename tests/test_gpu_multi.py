@@ -125,7 +125,7 @@ def _check(tmp_path, world, n):
 
 # the tile records of the fused gather depend on the tile size (variant) and on the world size (slot stride, flag and
 # acknowledgement arrays, peer stores per ballot word)
-CASES = [(2, None), (2, "t224"), (2, "t128"), (2, "t32"), (4, None), (4, "t64"), (8, None), (8, "t192")]
+CASES = [(2, None), (2, "t224"), (2, "t128g2"), (2, "t32"), (4, None), (4, "t64g2"), (8, None), (8, "t192g2")]
 
 
 @pytest.mark.parametrize("world,variant", CASES)

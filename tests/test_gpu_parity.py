@@ -147,7 +147,7 @@ def test_1m_adversarial_fleet(clf, g2):
     assert fr.exit_code == 0
 
 
-@pytest.mark.parametrize("variant", ["t224", "t192", "t128s3", "t128", "t64", "t32"])
+@pytest.mark.parametrize("variant", ["t256g2", "t192g2", "t128g2", "t64g2", "t32", "t224", "t128s3", "t64"])
 def test_every_kernel_variant(g2, variant, monkeypatch):
     """Each tile shape, on a fleet with rows too large to stage (read straight from global memory)."""
     tmpl, rows, truth, _ = g2

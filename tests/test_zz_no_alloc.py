@@ -74,7 +74,7 @@ def test_static_scratch_entry_point_refuses_oversize_shards():
     rows = torch.zeros(4096, dtype=torch.uint8, device=dev)
     rp = torch.zeros(4096, dtype=torch.int32, device=dev)
     out = engine.DeviceResult.alloc(16, dev)
-    n = native.STATIC_MAX_TILES * 224 + 1                       # one node more than the array's descriptors cover
+    n = native.STATIC_MAX_TILES * 256 + 1                       # one node more than the array's descriptors cover (256-node tiles)
     big = engine.DeviceBatch(rows, rp, n, n * 200)
     rc, msg = _classify_static(lib, big, out)
     assert rc == -1 and "static scratch holds 65536" in msg, msg
