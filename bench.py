@@ -516,6 +516,8 @@ def run_b200(args):
     # the gather target holds the fleet-wide ordered index list and counts (north star: all-reduce of the
     # counts + all-gather-v of the compacted indices); per-node values stay on the rank that owns them
     fleet = engine.DeviceResult.alloc(n_total, dev, defer_cap=1, records=False) if world > 1 else None
+    if gather_kind == "fused":
+        clf.fleet_target(fleet)      # the gather target is known before the launches: classify + gather are one kernel
 
     def step():
         clf.classify(batch, out)
@@ -536,24 +538,49 @@ def run_b200(args):
     if sampler:
         sampler.start()
     launches0 = clf.launches
+    if gather_kind == "fused":
+        clf.fleet_timing()          # clears the in-kernel timing sums of the warm-up
     k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    if world > 1:
+        # A device-side rendezvous between the barrier and the timed region: the ranks' CPUs leave the barrier tens of
+        # microseconds apart, and with a step of ~0.1 ms that start-up skew would be charged to the first step of the
+        # slower ranks' peers (the fused gather waits for every rank).  Behind this all-reduce every rank's stream
+        # resumes at the same moment, with the timed launches already queued.
+        dist.all_reduce(torch.zeros(1, device=dev))
+    # Per-launch events (the roofline's kernel time) cost a few microseconds of stream time each.  At N = 1 that is
+    # under 1 % of a step and they stay; with the fused gather at N > 1 a step is one ~0.1 ms launch whose parts are
+    # timed inside the kernel (fused_gather below), so the timed region holds nothing but the launches.
+    per_launch = not (world > 1 and gather_kind == "fused")
     t_start.record()
     for i in range(args.steps):
-        k_ev[i][0].record()
+        if per_launch:
+            k_ev[i][0].record()
         clf.classify(batch, out)
-        k_ev[i][1].record()
+        if per_launch:
+            k_ev[i][1].record()
         if world > 1:
             clf.gather(out, fleet)
     t_end.record()
     barrier()
     total_ms = t_start.elapsed_time(t_end)
-    kern_ms = [a.elapsed_time(b) for a, b in k_ev]
-    # what follows each classify launch on the stream until the next one starts: the gather (N > 1) and launch gaps
-    tail_ms = [k_ev[i][1].elapsed_time(k_ev[i + 1][0]) for i in range(args.steps - 1)] or [0.0]
+    if per_launch:
+        kern_ms = [a.elapsed_time(b) for a, b in k_ev]
+        # what follows each classify launch on the stream until the next one starts: the gather (N > 1) and launch gaps
+        tail_ms = [k_ev[i][1].elapsed_time(k_ev[i + 1][0]) for i in range(args.steps - 1)] or [0.0]
+    else:
+        kern_ms, tail_ms = [total_ms / args.steps], [0.0]
     launches = clf.launches - launches0
     clocks = sampler.stop() if sampler else None
+    fleet_timing = None
+    if gather_kind == "fused":
+        ft = clf.fleet_timing()
+        t = torch.tensor([ft["wait_us"], ft["rebuild_us"], ft["rebuild_us_max"], ft["classify_us"]], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        fleet_timing = {"classify_us": float(t[3]), "flag_wait_us": float(t[0]), "rebuild_us": float(t[1]), "rebuild_us_longest": float(t[2]),
+                        "note": "in-kernel timestamps over the timed steps, slowest rank: what a CTA spends on average classifying its tiles, "
+                                "then waiting for every rank's flag, then rebuilding the fleet-wide list"}
     if world > 1:
         t = torch.tensor([total_ms, statistics.mean(kern_ms), statistics.mean(tail_ms)], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -643,12 +670,13 @@ def run_b200(args):
                    "parallelism": f"shard{world}", "kernel_variant": variant,
                    "collectives": {"none": "none",
                                    "nccl": "one ncclAllGather of per-rank (counts block + compacted indices) slots, then an unpack kernel",
-                                   "fused": "none after the kernel: classify stores per-tile GPU-node ballots, prefixes and the counts into every "
-                                            "rank's buffer over NVLink (peer stores), gather = flag wait + local rebuild of the index list"}[gather_kind]},
+                                   "fused": "none, and no second launch: classify stores per-tile GPU-node ballots, prefixes and the counts into every "
+                                            "rank's buffer over NVLink (peer stores) while it runs, then the same kernel waits for the ranks' flags and "
+                                            "rebuilds the fleet-wide index list locally"}[gather_kind]},
         "verified": verified,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": f"gnc::classify_kernel ({variant})",
-                     "kernel_ms": kern_mean, "after_kernel_ms": tail_mean, "algorithmic_bytes_per_launch": int(algo_bytes),
+                     "kernel_ms": kern_mean, "after_kernel_ms": tail_mean, "fused_gather": fleet_timing, "algorithmic_bytes_per_launch": int(algo_bytes),
                      "bytes_per_node": algo_bytes / n, "frac_of_8TBps": achieved / 8000.0},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }

@@ -126,6 +126,21 @@ int gnc_gather(gnc_ctx*, const gnc_result* local, const gnc_result* all, void* c
  * Returns an error (and leaves the NCCL path in place) where peer mapping is not available. */
 int gnc_fleet_enable(gnc_ctx*, uint32_t fleet_nodes_cap, void* cuda_stream);
 
+/* Optional, after gnc_fleet_enable: name the gather target (`all` of gnc_gather; indices + counts form) BEFORE
+ * the classify launches.  gnc_classify then also rebuilds the fleet-wide ordered list into it once its own
+ * tiles are done and every rank's records have arrived -- classification and gather are ONE kernel launch --
+ * and gnc_gather with that same target has nothing left to do.  Every rank must do the same (all name a target
+ * or none does: the ranks acknowledge each other's buffers in step).  NULL clears the target.  The buffers
+ * must stay valid until the launches that use them have finished. */
+int gnc_fleet_target(gnc_ctx*, const gnc_result* all);
+
+/* Diagnostics of the fused gather since the last call (synchronous; resets them), from in-kernel timestamps in
+ * ns: out[0] time CTAs spent, after their tiles, waiting for every rank's flag, summed over CTAs and launches;
+ * out[1] likewise the time they spent rebuilding the index list; out[2] the longest single rebuild; out[3] how
+ * many CTAs were added up (divide the sums by it); out[4] the time CTAs spent in the launch before that (their
+ * share of the classification), summed likewise; out[5..7] reserved. */
+int gnc_fleet_timing(gnc_ctx*, uint64_t out[8]);
+
 /* Same classification from HOST memory: copies the shard to the device in pipelined chunks,
  * classifies, and copies flags / GPU-node records / counts back to the caller's HOST buffers
  * (the gnc_batch / gnc_result pointers are host pointers here).  Blocks until the results are in

@@ -121,7 +121,193 @@ struct Params {
   uint32_t* fleet_peer[kFleetMaxWorld];      // peer-mapped slots [world][fleet_slot_u32] of this epoch's parity, per rank
   unsigned long long* fleet_flag[kFleetMaxWorld];  // peer-mapped arrival flags [world] of this parity, per rank
   const unsigned long long* fleet_ack;       // local: [world] epochs each peer has consumed
+  // Gather target known before the launch (gnc_fleet_target): the kernel goes on to rebuild the fleet-wide
+  // index list itself once its tiles are done -- classification and gather are then ONE launch.
+  uint32_t* fleet_out_idx;                   // null: the rebuild is left to gnc_gather
+  int64_t* fleet_out_counts;
+  uint32_t fleet_out_cap;
+  unsigned int* fleet_unpack_done;           // local: CTAs that have finished reading the slots
+  unsigned long long* fleet_ack_peer[kFleetMaxWorld];  // every rank's acknowledgement array (peer-mapped)
 };
+
+// ------------------------------------------------------------------------------------------------
+// Rebuild of the fleet-wide ordered index list from the tile records all ranks stored here (fused gather).
+// Called by every thread of every CTA of a grid: by the classify kernel's own CTAs once their tiles are done,
+// or by fleet_unpack_kernel when the gather target was not known at launch.
+//   1. wait until every rank's slot of this epoch has arrived in the LOCAL fleet buffer (flags);
+//   2. a half-warp takes a group of whole tiles of one rank, up to 16 ballot words: one word per lane, each
+//      word's place from its tile's prefix and a segmented scan of the popcounts; the group's indices are one
+//      contiguous piece of the output, assembled in shared memory and stored coalesced; the next group's words
+//      are requested before this one's are expanded;
+//   3. the counts blocks are added up (one thread per slot), and the last CTA tells every rank that its slot
+//      here was consumed.
+// `buf` is 1024 words of shared memory per warp, `sh` 64 words of shared memory per CTA.
+// ------------------------------------------------------------------------------------------------
+struct FleetUnpack {
+  const uint32_t* slots;             // [world][slot_u32] this epoch's parity of the local fleet buffer
+  const unsigned long long* flags;   // [world] arrival flags of this parity
+  unsigned long long epoch;
+  int world, rank;
+  uint32_t slot_u32, cap;
+  uint32_t* out_idx;
+  uint32_t out_cap;
+  int64_t* out_counts;
+  unsigned int* done;
+  unsigned long long* const* ack_peer;  // [world]
+  unsigned long long* timing;           // [8] ns: sum of flag waits, sum of rebuild times, longest rebuild; CTAs added up; sum of t_before
+  unsigned long long t_before;          // ns this CTA spent in the launch before it came here (its share of the classification)
+};
+
+__device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf, unsigned long long* sh) {
+  unsigned long long* off = sh;                         // [world + 1] GPU nodes before each rank
+  unsigned long long* goff = sh + kFleetMaxWorld + 1;   // [world + 1] groups before each rank
+  int* timed_out = reinterpret_cast<int*>(sh + 2 * (kFleetMaxWorld + 1));
+  uint32_t* hdr = reinterpret_cast<uint32_t*>(sh + 2 * (kFleetMaxWorld + 1) + 1);  // [world][4]: tile nodes, tiles, node base, tiles per group
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, n_warps_cta = blockDim.x >> 5;
+  const unsigned long long t_enter = global_ns();
+  if (tid == 0) *timed_out = 0;
+  __syncthreads();
+  if (tid < u.world) {
+    const unsigned long long t0 = global_ns();
+    while (ld_sys_u64(u.flags + tid) < u.epoch)
+      if (global_ns() - t0 > kFleetTimeoutNs) {
+        *timed_out = 1;
+        break;
+      }
+  }
+  __syncthreads();
+  __threadfence_system();
+  const unsigned long long t_flags = global_ns();
+  // A group is up to 16 ballot words of whole tiles of one rank, handled by a half-warp (a lane per word): finer
+  // than a warp's 32 words, so that the ~10^4 groups of a 10M-node fleet spread evenly over the grid's warps.
+  auto tiles_per_group = [](uint32_t wpt) { return wpt >= 16u ? 1u : 16u / max(wpt, 1u); };
+  if (tid < u.world) {  // every rank's header words, read once
+    const uint32_t* h = u.slots + (size_t)tid * u.slot_u32;
+    const uint32_t tn = __ldcv(h + FLEET_H_TILE_NODES);
+    hdr[4 * tid + 0] = tn;
+    hdr[4 * tid + 1] = __ldcv(h + FLEET_H_TILES);
+    hdr[4 * tid + 2] = __ldcv(h + FLEET_H_NODE_BASE);
+    hdr[4 * tid + 3] = tiles_per_group(tn / 32);
+    off[tid + 1] = (unsigned long long)__ldcv(reinterpret_cast<const long long*>(h) + GNC_C_GPU_NODES);
+    if (tn / 32 > 16u) *timed_out = 1;  // tiles wider than a half-warp's 16 words: no kernel variant writes them
+  }
+  __syncthreads();
+  if (tid == 0) {
+    off[0] = goff[0] = 0;
+    for (int r = 0; r < u.world; r++) {
+      off[r + 1] += off[r];
+      goff[r + 1] = goff[r] + (hdr[4 * r + 1] + hdr[4 * r + 3] - 1) / hdr[4 * r + 3];
+    }
+  }
+  __syncthreads();
+  const int hl = lane & 15, half = lane >> 4;                  // lane within the half-warp, which half
+  uint32_t* mybuf = buf + (size_t)warp * 1024 + half * 512;
+  const unsigned long long n_halves = 2ull * gridDim.x * n_warps_cta, n_groups = goff[u.world];
+  // what a lane needs for group `grp`: its ballot word and its tile's prefix
+  struct Piece {
+    uint32_t m, pf, node0;  // ballot word, tile prefix, first node of the word
+    int r;
+    bool have;
+  };
+  auto fetch = [&](unsigned long long grp) {
+    Piece pc;
+    pc.m = pc.pf = pc.node0 = 0;
+    pc.r = 0;
+    pc.have = false;
+    if (grp >= n_groups) return pc;
+    int r = 0;
+    while (grp >= goff[r + 1]) r++;
+    const uint32_t* h = u.slots + (size_t)r * u.slot_u32;
+    const uint32_t tn = hdr[4 * r], wpt = tn / 32, tiles = hdr[4 * r + 1], tpg = hdr[4 * r + 3];
+    const uint32_t tl = wpt ? hl / wpt : 0u, w = wpt ? hl % wpt : 0u;
+    const unsigned long long tile = (grp - goff[r]) * tpg + tl;
+    pc.r = r;
+    pc.have = wpt != 0u && wpt <= 16u && tl < tpg && tile < tiles && (tile + 1) * (wpt + 1) <= u.cap;
+    if (pc.have) {
+      const uint32_t* rec = h + kFleetHeader + (size_t)tile * (wpt + 1);
+      pc.m = __ldcv(rec + 1 + w);
+      pc.pf = __ldcv(rec);
+      pc.node0 = hdr[4 * r + 2] + (uint32_t)tile * tn + 32u * w;
+    }
+    return pc;
+  };
+  // Groups are taken kBatch at a time: their words are all requested before the first is expanded, so a half-warp
+  // pays the trip to L2 once per batch, not once per group (the expansion itself is a fraction of that trip).
+  constexpr int kBatch = 4;
+  unsigned long long grp = 2ull * ((unsigned long long)blockIdx.x * n_warps_cta + warp) + half;
+  while (__any_sync(0xFFFFFFFFu, grp < n_groups)) {  // the two halves of a warp run their groups side by side
+    Piece pcs[kBatch];
+#pragma unroll
+    for (int i = 0; i < kBatch; i++) pcs[i] = fetch(grp + (unsigned long long)i * n_halves);
+#pragma unroll
+    for (int i = 0; i < kBatch; i++) {
+      const Piece cur = pcs[i];
+      const uint32_t cnt = cur.have ? __popc(cur.m) : 0u;
+      uint32_t incl = cnt;
+#pragma unroll
+      for (int d = 1; d < 16; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d, 16);
+        if (hl >= d) incl += t;
+      }
+      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 15, 16);
+      // tiles of a group follow one another in the output: the group's piece starts at its first tile's prefix
+      const uint32_t pf0 = __shfl_sync(0xFFFFFFFFu, cur.pf, 0, 16);
+      // the lane's word, bit by bit with no loop-carried dependence: bit b goes to (bits below b that are set)
+      const uint32_t at = incl - cnt, mm = cur.have ? cur.m : 0u;
+#pragma unroll
+      for (int b = 0; b < 32; b++)
+        if ((mm >> b) & 1u) mybuf[at + __popc(mm & ((1u << b) - 1u))] = cur.node0 + b;
+      __syncwarp();
+      const unsigned long long o0 = off[cur.r] + pf0;  // (cur.r is the same in every lane of the half)
+      if (o0 + total <= u.out_cap) {
+#pragma unroll 4
+        for (uint32_t k = hl; k < total; k += 16) u.out_idx[o0 + k] = mybuf[k];
+      } else {
+        for (uint32_t k = hl; k < total; k += 16)
+          if (o0 + k < u.out_cap) u.out_idx[o0 + k] = mybuf[k];
+      }
+      __syncwarp();
+    }
+    grp += (unsigned long long)kBatch * n_halves;
+  }
+  if (blockIdx.x == 0 && tid < GNC_N_COUNTS) {  // the all-reduce of the counts: exact sums, 128-bit for the key totals
+    const int sl = tid;
+    long long sum = 0;
+    if (sl >= GNC_C_KEY_LO && sl < GNC_C_KEY_HI + 4) {
+      const int k = (sl - GNC_C_KEY_LO) & 3;
+      unsigned __int128 key = 0;
+      for (int r = 0; r < u.world; r++) {
+        const long long* cr = reinterpret_cast<const long long*>(u.slots + (size_t)r * u.slot_u32);
+        key += ((unsigned __int128)(unsigned long long)__ldcv(cr + GNC_C_KEY_HI + k) << 64) | (unsigned long long)__ldcv(cr + GNC_C_KEY_LO + k);
+      }
+      sum = sl < GNC_C_KEY_HI ? (long long)(unsigned long long)key : (long long)(unsigned long long)(key >> 64);
+    } else {
+      for (int r = 0; r < u.world; r++) sum += __ldcv(reinterpret_cast<const long long*>(u.slots + (size_t)r * u.slot_u32) + sl);
+      if (sl == GNC_C_OUT_DROPPED) {
+        if (off[u.world] > u.out_cap) sum += (long long)(off[u.world] - u.out_cap);
+        if (*timed_out) sum += 1ll << 41;
+      }
+    }
+    u.out_counts[sl] = sum;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned long long t_done = global_ns();
+    if (u.timing) {  // sums over CTAs and launches (the host divides), and how many CTAs were added up
+      atomicAdd(u.timing + 0, t_flags - t_enter);
+      atomicAdd(u.timing + 1, t_done - t_flags);
+      atomicMax(u.timing + 2, t_done - t_flags);
+      atomicAdd(u.timing + 3, 1ull);
+      atomicAdd(u.timing + 4, u.t_before);
+    }
+    __threadfence();
+    if (atomicAdd(u.done, 1u) == gridDim.x - 1) {  // every CTA has read the slots: peers may overwrite them
+      *u.done = 0;
+      __threadfence_system();
+      for (int q = 0; q < u.world; q++) st_sys_u64(u.ack_peer[q] + u.rank, u.epoch);
+    }
+  }
+}
 
 __constant__ uint32_t c_nd_runs[GNC_ND_RUNS] = {GNC_ND_RUN_LIST};
 __constant__ uint32_t c_wide_spaces[GNC_WIDE_SPACES] = {GNC_WIDE_SPACE_LIST};
@@ -640,6 +826,7 @@ struct Smem {
   uint32_t direct[STAGES];  // 1: tile too large to stage, rows are read from global memory
   alignas(16) int part[kRing][TN / 32][P_N];
   uint32_t warp_base[kRing][TN / 32];
+  uint32_t ballot[kRing][TN / 32];  // the walker warps' GPU-node ballots (fused gather: the scan warp sends the tile's record)
   int scan_tile[kRing];
   uint32_t tile_cnt[kRing];  // [31:16] walker warps done with the tile, [15:0] GPU nodes counted so far
   alignas(8) uint2 stash_vals[kRing][TN];  // int16 x 4 per node
@@ -670,6 +857,7 @@ __global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_
   static_assert(kBarCnt + kRing <= 16, "named barrier ids");
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
+  const unsigned long long t_cta = FLEET ? global_ns() : 0ull;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; s++)
@@ -817,8 +1005,15 @@ __global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_
       const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, kWalkWarps - 1);
       const uint32_t excl = lookback(p, tile, total, lane);
       if (lane < kWalkWarps) sm.warp_base[b][lane] = excl + incl - c;
-      if (FLEET && lane < (int)p.fleet_world && (uint32_t)(tile + 1) * (kWalkWarps + 1) <= p.fleet_cap)  // one lane per peer
-        p.fleet_peer[lane][p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1)] = excl;
+      if (FLEET && (uint32_t)(tile + 1) * (kWalkWarps + 1) <= p.fleet_cap) {
+        // the tile's record -- its exclusive prefix, then its warps' ballots -- into every rank's buffer: a lane per
+        // (rank, word), so a rank gets its 4 (kWalkWarps + 1) bytes as one contiguous run of stores over NVLink
+        const uint32_t base = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1);
+        for (uint32_t idx = lane; idx < p.fleet_world * (kWalkWarps + 1); idx += 32) {
+          const uint32_t q = idx / (kWalkWarps + 1), w = idx - q * (kWalkWarps + 1);
+          p.fleet_peer[q][base + w] = w ? sm.ballot[b][w - 1] : excl;
+        }
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.pref_full[b]);
       GNC_T(6, it, gtimer());
@@ -955,10 +1150,7 @@ __global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_
         pp[0] = make_int4(__popc(gb), (int)n_ready, (int)n_def, (int)n_bad);  // P_GPU, P_READY, P_DEFERRED, P_MALFORMED
         pp[1] = make_int4(s0, s1, s2, s3);                                     // P_KEY0 ..
         if (wg == 0) sm.scan_tile[b] = tile;
-        if (FLEET && (uint32_t)(tile + 1) * (kWalkWarps + 1) <= p.fleet_cap) {
-          const uint32_t at = p.fleet_rank * p.fleet_slot_u32 + kFleetHeader + (uint32_t)tile * (kWalkWarps + 1) + 1 + wg;
-          for (uint32_t q = 0; q < p.fleet_world; q++) p.fleet_peer[q][at] = gb;
-        }
+        if (FLEET) sm.ballot[b][wg] = gb;
         // the last warp to count its share publishes the tile's aggregate at once: other CTAs'
         // look-backs must never wait for this CTA's scan warp to get round to the tile
         const uint32_t old = atomicAdd(&sm.tile_cnt[b], (uint32_t)__popc(gb) | (1u << 16));
@@ -1064,6 +1256,29 @@ __global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_
       __threadfence();
       sc->done = 0;
     }
+  }
+  if (FLEET && p.fleet_out_idx) {
+    // The gather, in the same launch: every rank's records for this epoch land in the local buffer while the
+    // kernels run; once they are all here (flags), this grid rebuilds the fleet-wide list.  The stages are free
+    // by now (every bulk copy was waited for by the walkers that used it): they serve as the warps' buffers.
+    __syncthreads();
+    static_assert((size_t)STAGES * (STAGE_BYTES + 32) >= (size_t)(cta_threads<TN, GROUPS>() / 32) * 4096, "a 4 KB buffer per warp inside the stages");
+    FleetUnpack u;
+    u.slots = p.fleet_peer[p.fleet_rank];
+    u.flags = p.fleet_flag[p.fleet_rank];
+    u.epoch = p.fleet_epoch;
+    u.world = (int)p.fleet_world;
+    u.rank = (int)p.fleet_rank;
+    u.slot_u32 = p.fleet_slot_u32;
+    u.cap = p.fleet_cap;
+    u.out_idx = p.fleet_out_idx;
+    u.out_cap = p.fleet_out_cap;
+    u.out_counts = p.fleet_out_counts;
+    u.done = p.fleet_unpack_done;
+    u.ack_peer = p.fleet_ack_peer;
+    u.timing = reinterpret_cast<unsigned long long*>(p.fleet_unpack_done) + 8;  // the spare words after the counter
+    u.t_before = global_ns() - t_cta;
+    fleet_unpack(u, reinterpret_cast<uint32_t*>(&sm.stage[0][0]), reinterpret_cast<unsigned long long*>(&sm.rp[0][0]));
   }
   if (tid == 0) GNC_T(7, 3, gtimer());  // CTA exit
 }

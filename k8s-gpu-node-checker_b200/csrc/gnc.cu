@@ -103,6 +103,11 @@ struct gnc_ctx {
     uint32_t shard_nodes = 0;              // the largest shard a slot has room for
     unsigned long long epoch = 0;
     unsigned int* unpack_done = nullptr;
+    // gnc_fleet_target: where the fleet-wide list goes, known before the classify launch
+    uint32_t* target_idx = nullptr;
+    int64_t* target_counts = nullptr;
+    uint32_t target_cap = 0;
+    unsigned long long unpacked_epoch = 0;  // the epoch whose classify launch did the rebuild itself
   } fleet;
   void* json_scratch = nullptr;     // gnc_json_to_pnl working arrays
   size_t json_scratch_bytes = 0;
@@ -191,6 +196,12 @@ void fleet_params(gnc_ctx* c, Params* p) {
     p->fleet_flag[q] = (unsigned long long*)(f.base[q] + 2 * f.region_bytes) + parity * c->world;
   }
   p->fleet_ack = (const unsigned long long*)(f.base[c->rank] + 2 * f.region_bytes + 2 * (size_t)c->world * 8);
+  p->fleet_out_idx = f.target_idx;
+  p->fleet_out_counts = f.target_counts;
+  p->fleet_out_cap = f.target_cap;
+  p->fleet_unpack_done = f.unpack_done;
+  for (int q = 0; q < c->world; q++)
+    p->fleet_ack_peer[q] = (unsigned long long*)(f.base[q] + 2 * f.region_bytes + 2 * (size_t)c->world * 8);
 }
 
 __global__ void fleet_publish_empty_kernel(const Params p) {
@@ -211,108 +222,30 @@ struct AckPtrs {
   unsigned long long* p[gnc::kFleetMaxWorld];
 };
 
-// Wait until every rank's slot of this epoch has arrived in the LOCAL fleet buffer, then rebuild the dense
-// rank-ordered index list from the tile records (prefix + GPU-node ballots) and sum the counts, then tell
-// every rank that its slot here was consumed.  A warp takes 32 consecutive ballot words of one rank: their
-// indices are one contiguous piece of the output, assembled in shared memory and stored coalesced.
+// The rebuild as a launch of its own (gnc_gather when the target was not given to the classify launch,
+// empty shards): see gnc::fleet_unpack in classify.cuh.
 constexpr int kUnpackWarps = 8;
 __global__ void __launch_bounds__(kUnpackWarps * 32) fleet_unpack_kernel(
     const uint32_t* slots, const unsigned long long* flags, unsigned long long epoch, int world, int rank, uint32_t slot_u32, uint32_t cap,
     uint32_t* out_idx, uint32_t out_cap, int64_t* out_counts, unsigned int* done, AckPtrs ack_peer) {
-  __shared__ unsigned long long off[gnc::kFleetMaxWorld + 1];   // GPU nodes before each rank
-  __shared__ unsigned long long goff[gnc::kFleetMaxWorld + 1];  // 32-word groups before each rank
-  __shared__ uint32_t buf[kUnpackWarps][1024];
-  __shared__ int timed_out;
-  if (threadIdx.x == 0) timed_out = 0;
-  __syncthreads();
-  if (threadIdx.x < world) {
-    const unsigned long long t0 = gnc::global_ns();
-    while (gnc::ld_sys_u64(flags + threadIdx.x) < epoch)
-      if (gnc::global_ns() - t0 > gnc::kFleetTimeoutNs) {
-        timed_out = 1;
-        break;
-      }
-  }
-  __syncthreads();
-  __threadfence_system();
-  if (threadIdx.x == 0) {
-    off[0] = goff[0] = 0;
-    for (int r = 0; r < world; r++) {
-      const uint32_t* h = slots + (size_t)r * slot_u32;
-      const unsigned long long words = (unsigned long long)__ldcv(h + gnc::FLEET_H_TILES) * (__ldcv(h + gnc::FLEET_H_TILE_NODES) / 32);
-      off[r + 1] = off[r] + (unsigned long long)__ldcv(reinterpret_cast<const long long*>(h) + GNC_C_GPU_NODES);
-      goff[r + 1] = goff[r] + (words + 31) / 32;
-    }
-  }
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const unsigned long long n_warps = (unsigned long long)gridDim.x * kUnpackWarps;
-  for (unsigned long long grp = (unsigned long long)blockIdx.x * kUnpackWarps + warp; grp < goff[world]; grp += n_warps) {
-    int r = 0;
-    while (grp >= goff[r + 1]) r++;
-    const uint32_t* h = slots + (size_t)r * slot_u32;
-    const uint32_t tn = __ldcv(h + gnc::FLEET_H_TILE_NODES), wpt = tn / 32, tiles = __ldcv(h + gnc::FLEET_H_TILES);
-    const uint32_t node_base = __ldcv(h + gnc::FLEET_H_NODE_BASE);
-    const unsigned long long words = (unsigned long long)tiles * wpt, j = (grp - goff[r]) * 32 + lane;
-    const uint32_t tile = (uint32_t)(j / wpt), w = (uint32_t)(j % wpt);
-    const uint32_t* rec = h + gnc::kFleetHeader + (size_t)tile * (wpt + 1);
-    const bool have = j < words && (unsigned long long)(tile + 1) * (wpt + 1) <= cap;
-    const uint32_t m = have ? __ldcv(rec + 1 + w) : 0u;
-    const uint32_t cnt = __popc(m);
-    // where the group starts in the rank's list: the first word's tile prefix + the GPU nodes of the tile's earlier warps
-    uint32_t start = 0;
-    if (lane == 0 && have) {
-      start = __ldcv(rec);
-      for (uint32_t u = 0; u < w; u++) start += __popc(__ldcv(rec + 1 + u));
-    }
-    start = __shfl_sync(0xFFFFFFFFu, start, 0);
-    uint32_t incl = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-      if (lane >= d) incl += t;
-    }
-    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-    uint32_t at = incl - cnt, mm = m;
-    const uint32_t node0 = node_base + tile * tn + 32 * w;
-    while (mm) {
-      buf[warp][at++] = node0 + (__ffs(mm) - 1);
-      mm &= mm - 1;
-    }
-    __syncwarp();
-    const unsigned long long o0 = off[r] + start;
-    for (uint32_t k = lane; k < total; k += 32)
-      if (o0 + k < out_cap) out_idx[o0 + k] = buf[warp][k];
-    __syncwarp();
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    long long sum[GNC_N_COUNTS];
-    unsigned __int128 key[4] = {0, 0, 0, 0};
-    unsigned long long lost = 0;
-    for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] = 0;
-    for (int r = 0; r < world; r++) {
-      const long long* cr = reinterpret_cast<const long long*>(slots + (size_t)r * slot_u32);
-      for (int s = 0; s < GNC_N_COUNTS; s++) sum[s] += cr[s];
-      for (int k = 0; k < 4; k++)
-        key[k] += ((unsigned __int128)(unsigned long long)cr[GNC_C_KEY_HI + k] << 64) | (unsigned long long)cr[GNC_C_KEY_LO + k];
-    }
-    if (off[world] > out_cap) lost = max(lost, off[world] - out_cap);
-    for (int k = 0; k < 4; k++) {
-      sum[GNC_C_KEY_LO + k] = (long long)(unsigned long long)key[k];
-      sum[GNC_C_KEY_HI + k] = (long long)(unsigned long long)(key[k] >> 64);
-    }
-    sum[GNC_C_OUT_DROPPED] += (long long)lost + (timed_out ? (1ll << 41) : 0);
-    for (int s = 0; s < GNC_N_COUNTS; s++) out_counts[s] = sum[s];
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    if (atomicAdd(done, 1u) == gridDim.x - 1) {  // every block has read the slots: peers may overwrite them
-      *done = 0;
-      __threadfence_system();
-      for (int q = 0; q < world; q++) gnc::st_sys_u64(ack_peer.p[q] + rank, epoch);
-    }
-  }
+  __shared__ uint32_t buf[kUnpackWarps * 1024];
+  __shared__ unsigned long long sh[64];
+  gnc::FleetUnpack u;
+  u.slots = slots;
+  u.flags = flags;
+  u.epoch = epoch;
+  u.world = world;
+  u.rank = rank;
+  u.slot_u32 = slot_u32;
+  u.cap = cap;
+  u.out_idx = out_idx;
+  u.out_cap = out_cap;
+  u.out_counts = out_counts;
+  u.done = done;
+  u.ack_peer = ack_peer.p;
+  u.timing = reinterpret_cast<unsigned long long*>(done) + 8;
+  u.t_before = 0;
+  gnc::fleet_unpack(u, buf, sh);
 }
 
 }  // namespace
@@ -386,7 +319,7 @@ int classify_impl(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* 
     CUDA_TRY(c, cudaMemsetAsync(out->counts, 0, GNC_N_COUNTS * sizeof(int64_t), stream));
     if (c->fleet.on) {  // an empty shard still has to tell the other ranks so
       Params p = {};
-      fleet_params(c, &p);
+      fleet_params(c, &p);  // (the rebuild of this epoch is then gnc_gather's: unpacked_epoch stays behind)
       fleet_publish_empty_kernel<<<1, 32, 0, stream>>>(p);
       CUDA_TRY(c, cudaGetLastError());
       c->launches++;
@@ -434,8 +367,12 @@ int classify_impl(gnc_ctx* c, const gnc_batch* in, const gnc_result* out, void* 
     fleet_params(c, &p);
   }
   const int grid = (int)std::min<uint32_t>(tiles, (uint32_t)(c->sm_count * c->ctas_per_sm[v]));
-  if (c->fleet.on) var.launch_fleet(p, grid, var.smem, stream);
-  else var.launch(p, grid, var.smem, stream);
+  if (c->fleet.on) {
+    var.launch_fleet(p, grid, var.smem, stream);
+    if (p.fleet_out_idx) c->fleet.unpacked_epoch = p.fleet_epoch;
+  } else {
+    var.launch(p, grid, var.smem, stream);
+  }
   CUDA_TRY(c, cudaGetLastError());
   c->launches++;
   return GNC_OK;
@@ -931,6 +868,32 @@ extern "C" int gnc_fleet_enable(gnc_ctx* c, uint32_t fleet_nodes_cap, void* cuda
   return GNC_OK;
 }
 
+extern "C" int gnc_fleet_target(gnc_ctx* c, const gnc_result* all) {
+  if (!c) return GNC_ERR_ARG;
+  gnc_ctx::Fleet& f = c->fleet;
+  if (!all) {
+    f.target_idx = nullptr;
+    f.target_counts = nullptr;
+    f.target_cap = 0;
+    return GNC_OK;
+  }
+  if (!all->gpu_idx || !all->counts) return fail(c, GNC_ERR_ARG, "gnc_fleet_target: gpu_idx or counts is null");
+  f.target_idx = all->gpu_idx;
+  f.target_counts = all->counts;
+  f.target_cap = all->out_cap;
+  return GNC_OK;
+}
+
+extern "C" int gnc_fleet_timing(gnc_ctx* c, uint64_t out[8]) {
+  if (!c || !out) return GNC_ERR_ARG;
+  if (!c->fleet.on) return fail(c, GNC_ERR_STATE, "the fused gather is not enabled");
+  CUDA_TRY(c, cudaSetDevice(c->device));
+  unsigned long long* t = reinterpret_cast<unsigned long long*>(c->fleet.unpack_done) + 8;
+  CUDA_TRY(c, cudaMemcpy(out, t, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  CUDA_TRY(c, cudaMemset(t, 0, 8 * sizeof(uint64_t)));
+  return GNC_OK;
+}
+
 extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result* all, void* cuda_stream) {
   if (!c) return GNC_ERR_ARG;
   if (!local || !all || !local->counts || !all->counts) return fail(c, GNC_ERR_ARG, "null result or counts");
@@ -949,6 +912,8 @@ extern "C" int gnc_gather(gnc_ctx* c, const gnc_result* local, const gnc_result*
     // the slots into the dense rank-ordered list, add the counts up, acknowledge.  No collective.
     if (!all->gpu_idx) return fail(c, GNC_ERR_ARG, "gpu_idx is null");
     gnc_ctx::Fleet& f = c->fleet;
+    if (f.unpacked_epoch == f.epoch && f.target_idx == all->gpu_idx && f.target_counts == all->counts && f.target_cap == all->out_cap)
+      return GNC_OK;  // the classify launch of this epoch has rebuilt the list into this very target already
     const size_t parity = f.epoch & 1;
     AckPtrs ap = {};
     for (int q = 0; q < c->world; q++) ap.p[q] = (unsigned long long*)(f.base[q] + 2 * f.region_bytes + 2 * (size_t)c->world * 8);

@@ -184,6 +184,24 @@ class Classifier:
         s = stream or torch.cuda.current_stream(self.device)
         self._check(self.lib.gnc_fleet_enable(self._h, fleet_nodes_cap, ctypes.c_void_p(s.cuda_stream)))
 
+    def fleet_target(self, fleet: Optional[DeviceResult]):
+        """Name the gather target before the classify launches: classify then does the gather in the same launch
+        (every rank must do likewise).  `None` clears it."""
+        if fleet is None:
+            self._check(self.lib.gnc_fleet_target(self._h, None))
+        else:
+            self._fleet_target = fleet                                  # keep the buffers alive
+            r = fleet.c_struct()
+            self._check(self.lib.gnc_fleet_target(self._h, ctypes.byref(r)))
+
+    def fleet_timing(self) -> Dict[str, float]:
+        """Mean flag wait and mean / longest rebuild time per CTA (us) since the last call (in-kernel timestamps)."""
+        t = (ctypes.c_uint64 * 8)()
+        self._check(self.lib.gnc_fleet_timing(self._h, t))
+        k = max(1, int(t[3]))
+        return {"wait_us": t[0] / k / 1e3, "rebuild_us": t[1] / k / 1e3, "rebuild_us_max": t[2] / 1e3, "ctas": int(t[3]),
+                "classify_us": t[4] / k / 1e3}
+
     def gather(self, local: DeviceResult, fleet: DeviceResult, stream: Optional[torch.cuda.Stream] = None) -> DeviceResult:
         s = stream or torch.cuda.current_stream(self.device)
         a, b = local.c_struct(), fleet.c_struct()

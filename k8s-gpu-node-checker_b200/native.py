@@ -38,7 +38,7 @@ class JsonOut(ctypes.Structure):
 
 
 EXPORTS = ("gnc_abi_version", "gnc_create", "gnc_comm_id", "gnc_reserve", "gnc_set_max_str_digits", "gnc_classify",
-           "gnc_gather", "gnc_fleet_enable", "gnc_classify_host", "gnc_classify_static", "gnc_json_to_pnl", "gnc_launch_count", "gnc_variant_for", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
+           "gnc_gather", "gnc_fleet_enable", "gnc_fleet_target", "gnc_fleet_timing", "gnc_classify_host", "gnc_classify_static", "gnc_json_to_pnl", "gnc_launch_count", "gnc_variant_for", "gnc_unicode_tables", "gnc_last_error", "gnc_destroy")
 
 
 class GncError(RuntimeError):
@@ -89,6 +89,10 @@ def lib() -> ctypes.CDLL:
     L.gnc_classify_host.argtypes = [vp, ctypes.POINTER(Batch), ctypes.POINTER(Result)]
     L.gnc_fleet_enable.argtypes = [vp, u32, vp]
     L.gnc_fleet_enable.restype = i32
+    L.gnc_fleet_target.argtypes = [vp, ctypes.POINTER(Result)]
+    L.gnc_fleet_target.restype = i32
+    L.gnc_fleet_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_uint64)]
+    L.gnc_fleet_timing.restype = i32
     L.gnc_classify_static.argtypes = [i32, ctypes.POINTER(Batch), ctypes.POINTER(Result), i32, vp, ctypes.c_char_p,
                                       ctypes.c_size_t]
     L.gnc_classify_static.restype = i32

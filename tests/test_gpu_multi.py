@@ -92,6 +92,31 @@ def _worker(rank, world, port, n, out_dir, short_by):
         torch.cuda.synchronize()
         assert int(small.counts[14]) == short_by and int(small.counts[0]) == g
         assert torch.equal(small.gpu_idx[:g - short_by], fleet.gpu_idx[:g - short_by])
+    # the same with the target named before the launch: classify rebuilds the list itself, gather has nothing left to do
+    onek = engine.DeviceResult.alloc(n, dev, defer_cap=1, records=False)
+    clf.fleet_target(onek)
+    for _ in range(4):
+        onek.gpu_idx.fill_(-1)
+        onek.counts.fill_(-1)
+        before = clf.launches
+        clf.classify(batch, local)
+        clf.gather(local, onek)
+        torch.cuda.synchronize()
+        assert clf.launches - before == (1 if hi > lo else 2)           # one launch did both (an empty shard: its notice, then the rebuild)
+        assert torch.equal(onek.counts, fleet.counts), (onek.counts, fleet.counts)
+        assert torch.equal(onek.gpu_idx[:g], fleet.gpu_idx[:g])
+    clf.gather(local, fused)                                            # another target: the rebuild runs as a launch of its own
+    torch.cuda.synchronize()
+    assert torch.equal(fused.gpu_idx[:g], fleet.gpu_idx[:g])
+    if short_by and g > short_by:
+        small = engine.DeviceResult.alloc(n, dev, out_cap=g - short_by, defer_cap=1, records=False)
+        clf.fleet_target(small)
+        clf.classify(batch, local)
+        clf.gather(local, small)
+        torch.cuda.synchronize()
+        assert int(small.counts[14]) == short_by and int(small.counts[0]) == g
+        assert torch.equal(small.gpu_idx[:g - short_by], fleet.gpu_idx[:g - short_by])
+    clf.fleet_target(None)
     counts = fleet.counts.cpu().numpy()
     np.save(os.path.join(out_dir, f"c{rank}.npy"), counts)
     np.save(os.path.join(out_dir, f"i{rank}.npy"), fleet.gpu_idx.cpu().numpy().view(np.uint32)[:g])
