@@ -641,8 +641,8 @@ __device__ __forceinline__ void resolve_key(const uint8_t* buf, uint32_t s, uint
 //     condition of lengths 5 and 4) are pushed into small shift registers;
 //  2. look at the candidates' text, oldest first.  Every lane has about the same number of
 //     candidates, so the warp stays converged here whatever position the keys had in the rows.
-// Returns false when the row needs the general walk (extended form, misaligned or >= 64 KB row,
-// more candidates than the registers hold).
+// Returns false when the row needs the general walk (extended form, misaligned or >= 64 KB row, more
+// candidates than the registers hold, texts that run past the row).
 __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_t e, int max_digits, NodeResult& r) {
   r.v01 = r.v23 = 0;
   r.bits = 0;
@@ -680,50 +680,40 @@ __device__ __forceinline__ bool walk_row(const uint8_t* buf, uint32_t s, uint32_
     }
     rel += (hv & 0xFFu) + (hv >> 8);
   }
-  if (nk > 4u || nq > 2u || rel >= 65536u) return false;
-  const uint32_t row_len = e - s;
-  bool stop = false;
-  // capacity candidates, oldest first: bounds, then the first four key bytes.  The few that pass
-  // (one per GPU node) are resolved afterwards, so that lanes whose key sat at different candidate
-  // positions compare key tails and parse values together.
+  // A row whose texts do not all fit it (rel is where the last one would end) is malformed: the general walk
+  // knows what counts in such a row.  Past this line every entry lies inside the row, so no candidate needs a
+  // bounds check and the order of the candidates only matters for a key that appears twice.
+  if (nk > 4u || nq > 2u || rel > e - s) return false;
+  // capacity candidates, oldest first: the first four key bytes.  The few that pass (one per GPU node) are
+  // resolved afterwards, so that lanes whose key sat at different candidate positions compare key tails and
+  // parse values together.
   uint32_t real_a = 0, real_b = 0, n_real = 0;  // real_a older
 #pragma unroll
   for (int i = 3; i >= 0; --i) {
     const uint32_t rec = i == 3 ? k3 : i == 2 ? k2 : i == 1 ? k1 : k0;
-    if ((uint32_t)i < nk && !stop) {
+    if ((uint32_t)i < nk) {
       const uint32_t kl = rec & 0xFFu;
-      if ((rec >> 16) + kl + ((rec >> 8) & 0xFFu) > row_len) {
-        r.bits |= R_MALFORMED;  // the entry's text runs past the row: nothing after it counts
-        stop = true;
-      } else {
-        const uint32_t e0 = kl == 14u ? pack4("nvid", 0, 4) : kl == 11u ? pack4("amd.", 0, 4) : kl == 18u ? pack4("gpu.", 0, 4) : pack4("inte", 0, 4);
-        if (ld32u(buf, s + (rec >> 16)) == e0) {
-          real_a = real_b;
-          real_b = rec;
-          ++n_real;
-        }
+      const uint32_t e0 = kl == 14u ? pack4("nvid", 0, 4) : kl == 11u ? pack4("amd.", 0, 4) : kl == 18u ? pack4("gpu.", 0, 4) : pack4("inte", 0, 4);
+      if (ld32u(buf, s + (rec >> 16)) == e0) {
+        real_a = real_b;
+        real_b = rec;
+        ++n_real;
       }
     }
   }
   if (n_real > 2u) return false;
   if (n_real > 1u) resolve_key(buf, s, real_a, max_digits, r);
   if (n_real > 0u) resolve_key(buf, s, real_b, max_digits, r);
-  // condition candidates, oldest first: the first (Ready, True) ends the walk (check-gpu-node.py:176-177)
+  // condition candidates: any (Ready, True) will do (check-gpu-node.py:175-177)
 #pragma unroll
   for (int i = 1; i >= 0; --i) {
     const uint32_t rec = i == 1 ? q1 : q0;
-    if ((uint32_t)i < nq && !stop) {
+    if ((uint32_t)i < nq) {
       const uint32_t kp = s + (rec >> 16);
-      if ((rec >> 16) + 9u > row_len) {
-        r.bits |= R_MALFORMED;
-        stop = true;
-      } else if (ld32u(buf, kp) == pack4("Read", 0, 4) && ld32u(buf, kp + 4) == pack4("yTru", 0, 4) && (ld32u(buf, kp + 8) & 0xFFu) == 'e') {
+      if (ld32u(buf, kp) == pack4("Read", 0, 4) && ld32u(buf, kp + 4) == pack4("yTru", 0, 4) && (ld32u(buf, kp + 8) & 0xFFu) == 'e')
         r.bits |= R_READY;
-        stop = true;
-      }
     }
   }
-  if (!stop && rel > row_len) r.bits |= R_MALFORMED;  // some entry's text ran past the row
   return true;
 }
 
