@@ -578,7 +578,7 @@ def run_b200(args):
         ft = clf.fleet_timing()
         t = torch.tensor([ft["wait_us"], ft["rebuild_us"], ft["rebuild_us_max"], ft["classify_us"]], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        fleet_timing = {"classify_us": float(t[3]), "flag_wait_us": float(t[0]), "rebuild_us": float(t[1]), "rebuild_us_longest": float(t[2]),
+        fleet_timing = {"rebuild_header_us": ft["rebuild_header_us"], "rebuild_groups_us_warp0": ft["rebuild_groups_us"], "classify_us": float(t[3]), "flag_wait_us": float(t[0]), "rebuild_us": float(t[1]), "rebuild_us_longest": float(t[2]),
                         "note": "in-kernel timestamps over the timed steps, slowest rank: what a CTA spends on average classifying its tiles, "
                                 "then waiting for every rank's flag, then rebuilding the fleet-wide list"}
     if world > 1:

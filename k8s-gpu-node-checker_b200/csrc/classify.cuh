@@ -141,8 +141,13 @@ struct Params {
 //      are requested before this one's are expanded;
 //   3. the counts blocks are added up (one thread per slot), and the last CTA tells every rank that its slot
 //      here was consumed.
-// `buf` is 1024 words of shared memory per warp, `sh` 64 words of shared memory per CTA.
+// `buf` is 2 * kUnpackHalfWords words of shared memory per warp (16-byte aligned), `sh` 64 words and `lut` 256
+// words per CTA.
 // ------------------------------------------------------------------------------------------------
+// shared-memory words a half-warp's buffer takes: up to 512 indices + 3 of alignment shift, then a spare word for the
+// bits that are clear; a multiple of 4 so that every half's buffer is 16-byte aligned
+constexpr uint32_t kUnpackSpare = 516, kUnpackHalfWords = 520;
+
 struct FleetUnpack {
   const uint32_t* slots;             // [world][slot_u32] this epoch's parity of the local fleet buffer
   const unsigned long long* flags;   // [world] arrival flags of this parity
@@ -158,7 +163,57 @@ struct FleetUnpack {
   unsigned long long t_before;          // ns this CTA spent in the launch before it came here (its share of the classification)
 };
 
-__device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf, unsigned long long* sh) {
+// One group of the rebuild, by a half-warp (see fleet_unpack): a lane's ballot word `m` of a tile with prefix `pf`,
+// whose first node is node0; `base` = GPU nodes of the ranks before this one.  Both halves of the warp call together.
+__device__ __noinline__ void unpack_group(uint32_t* __restrict__ out_idx, uint32_t out_cap, uint32_t m, uint32_t pf, uint32_t node0, bool have,
+                                          unsigned long long base, uint32_t* mybuf, const uint32_t* __restrict__ lut, int hl) {
+  const uint32_t cnt = have ? __popc(m) : 0u;
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 16; d <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d, 16);
+    if (hl >= d) incl += t;
+  }
+  const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 15, 16);
+  // tiles of a group follow one another in the output: the group's piece starts at its first tile's prefix
+  const uint32_t pf0 = __shfl_sync(0xFFFFFFFFu, pf, 0, 16);
+  const unsigned long long o0 = base + pf0;
+  // The piece is laid out in the buffer as it will lie in memory modulo 16 bytes (buffer word i <-> output word
+  // o0 - shift + i), so that its aligned middle goes out as 16-byte stores.  The lane's word is expanded bit by
+  // bit with no branch and no loop-carried dependence: bit b goes to (bits below b that are set), a clear bit
+  // to a spare word.
+  const uint32_t shift = (uint32_t)((reinterpret_cast<uintptr_t>(out_idx + o0) >> 2) & 3u);  // (whatever the list's own alignment)
+  // (population counts per bit would do, but POPC issues at a quarter of the rate of the integer pipe and 31 of
+  // them per word were most of the rebuild's time: the table gives a byte's eight counts in one shared-memory load)
+  const uint32_t mm = have ? m : 0u;
+  const uint32_t l0 = lut[mm & 0xFFu], l1 = lut[(mm >> 8) & 0xFFu], l2 = lut[(mm >> 16) & 0xFFu], l3 = lut[mm >> 24];
+  const uint32_t at0 = shift + incl - cnt, at1 = at0 + (l0 >> 24), at2 = at1 + (l1 >> 24), at3 = at2 + (l2 >> 24);
+#pragma unroll
+  for (int b = 0; b < 32; b++) {
+    const uint32_t l = b < 8 ? l0 : b < 16 ? l1 : b < 24 ? l2 : l3, a = b < 8 ? at0 : b < 16 ? at1 : b < 24 ? at2 : at3;
+    const bool on = (mm >> b) & 1u;
+    mybuf[on ? a + ((l >> (3 * (b & 7))) & 7u) : kUnpackSpare] = node0 + b;
+  }
+  __syncwarp();
+  const uint32_t end = shift + total;  // buffer words [shift, end) are the piece
+  if (o0 + total <= out_cap) {
+    uint4* dst4 = reinterpret_cast<uint4*>(out_idx + (o0 - shift));
+    const uint4* src4 = reinterpret_cast<const uint4*>(mybuf);
+    for (uint32_t v = hl; 4u * v < end; v += 16) {
+      if (4u * v >= shift && 4u * v + 4u <= end) {
+        dst4[v] = src4[v];
+      } else {
+        for (uint32_t k = max(4u * v, shift); k < min(4u * v + 4u, end); k++) out_idx[o0 - shift + k] = mybuf[k];
+      }
+    }
+  } else {
+    for (uint32_t k = shift + hl; k < end; k += 16)
+      if (o0 - shift + k < out_cap) out_idx[o0 - shift + k] = mybuf[k];
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf, unsigned long long* sh, uint32_t* lut) {
   unsigned long long* off = sh;                         // [world + 1] GPU nodes before each rank
   unsigned long long* goff = sh + kFleetMaxWorld + 1;   // [world + 1] groups before each rank
   int* timed_out = reinterpret_cast<int*>(sh + 2 * (kFleetMaxWorld + 1));
@@ -166,6 +221,11 @@ __device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, n_warps_cta = blockDim.x >> 5;
   const unsigned long long t_enter = global_ns();
   if (tid == 0) *timed_out = 0;
+  for (int v = tid; v < 256; v += blockDim.x) {  // byte -> its eight "set bits below bit k" counts, 3 bits each, and its popcount << 24
+    uint32_t e = (uint32_t)__popc(v) << 24;
+    for (int k = 1; k < 8; k++) e |= (uint32_t)__popc(v & ((1 << k) - 1)) << (3 * k);
+    lut[v] = e;
+  }
   __syncthreads();
   if (tid < u.world) {
     const unsigned long long t0 = global_ns();
@@ -200,8 +260,9 @@ __device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf
     }
   }
   __syncthreads();
+  const unsigned long long t_hdr = global_ns();
   const int hl = lane & 15, half = lane >> 4;                  // lane within the half-warp, which half
-  uint32_t* mybuf = buf + (size_t)warp * 1024 + half * 512;
+  uint32_t* mybuf = buf + (size_t)warp * (2 * kUnpackHalfWords) + half * kUnpackHalfWords;
   const unsigned long long n_halves = 2ull * gridDim.x * n_warps_cta, n_groups = goff[u.world];
   // what a lane needs for group `grp`: its ballot word and its tile's prefix
   struct Piece {
@@ -240,36 +301,11 @@ __device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf
 #pragma unroll
     for (int i = 0; i < kBatch; i++) pcs[i] = fetch(grp + (unsigned long long)i * n_halves);
 #pragma unroll
-    for (int i = 0; i < kBatch; i++) {
-      const Piece cur = pcs[i];
-      const uint32_t cnt = cur.have ? __popc(cur.m) : 0u;
-      uint32_t incl = cnt;
-#pragma unroll
-      for (int d = 1; d < 16; d <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d, 16);
-        if (hl >= d) incl += t;
-      }
-      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 15, 16);
-      // tiles of a group follow one another in the output: the group's piece starts at its first tile's prefix
-      const uint32_t pf0 = __shfl_sync(0xFFFFFFFFu, cur.pf, 0, 16);
-      // the lane's word, bit by bit with no loop-carried dependence: bit b goes to (bits below b that are set)
-      const uint32_t at = incl - cnt, mm = cur.have ? cur.m : 0u;
-#pragma unroll
-      for (int b = 0; b < 32; b++)
-        if ((mm >> b) & 1u) mybuf[at + __popc(mm & ((1u << b) - 1u))] = cur.node0 + b;
-      __syncwarp();
-      const unsigned long long o0 = off[cur.r] + pf0;  // (cur.r is the same in every lane of the half)
-      if (o0 + total <= u.out_cap) {
-#pragma unroll 4
-        for (uint32_t k = hl; k < total; k += 16) u.out_idx[o0 + k] = mybuf[k];
-      } else {
-        for (uint32_t k = hl; k < total; k += 16)
-          if (o0 + k < u.out_cap) u.out_idx[o0 + k] = mybuf[k];
-      }
-      __syncwarp();
-    }
+    for (int i = 0; i < kBatch; i++)  // (one copy of the code, called: unrolled four times it overflows the instruction cache)
+      unpack_group(u.out_idx, u.out_cap, pcs[i].m, pcs[i].pf, pcs[i].node0, pcs[i].have, off[pcs[i].r], mybuf, lut, hl);
     grp += (unsigned long long)kBatch * n_halves;
   }
+  const unsigned long long t_loop = global_ns();
   if (blockIdx.x == 0 && tid < GNC_N_COUNTS) {  // the all-reduce of the counts: exact sums, 128-bit for the key totals
     const int sl = tid;
     long long sum = 0;
@@ -299,6 +335,8 @@ __device__ __forceinline__ void fleet_unpack(const FleetUnpack& u, uint32_t* buf
       atomicMax(u.timing + 2, t_done - t_flags);
       atomicAdd(u.timing + 3, 1ull);
       atomicAdd(u.timing + 4, u.t_before);
+      atomicAdd(u.timing + 5, t_hdr - t_flags);
+      atomicAdd(u.timing + 6, t_loop - t_hdr);   // (this thread's warp; the CTA's slowest warp shows in the total)
     }
     __threadfence();
     if (atomicAdd(u.done, 1u) == gridDim.x - 1) {  // every CTA has read the slots: peers may overwrite them
@@ -1252,7 +1290,7 @@ __global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_
     // kernels run; once they are all here (flags), this grid rebuilds the fleet-wide list.  The stages are free
     // by now (every bulk copy was waited for by the walkers that used it): they serve as the warps' buffers.
     __syncthreads();
-    static_assert((size_t)STAGES * (STAGE_BYTES + 32) >= (size_t)(cta_threads<TN, GROUPS>() / 32) * 4096, "a 4 KB buffer per warp inside the stages");
+    static_assert((size_t)STAGES * (STAGE_BYTES + 32) >= (size_t)(cta_threads<TN, GROUPS>() / 32) * 2 * kUnpackHalfWords * 4 + 1024, "a buffer per warp and the byte table inside the stages");
     FleetUnpack u;
     u.slots = p.fleet_peer[p.fleet_rank];
     u.flags = p.fleet_flag[p.fleet_rank];
@@ -1268,7 +1306,8 @@ __global__ void __launch_bounds__(cta_threads<TN, GROUPS>(), MIN_CTAS) classify_
     u.ack_peer = p.fleet_ack_peer;
     u.timing = reinterpret_cast<unsigned long long*>(p.fleet_unpack_done) + 8;  // the spare words after the counter
     u.t_before = global_ns() - t_cta;
-    fleet_unpack(u, reinterpret_cast<uint32_t*>(&sm.stage[0][0]), reinterpret_cast<unsigned long long*>(&sm.rp[0][0]));
+    uint32_t* ubuf = reinterpret_cast<uint32_t*>(&sm.stage[0][0]);
+    fleet_unpack(u, ubuf, reinterpret_cast<unsigned long long*>(&sm.rp[0][0]), ubuf + (size_t)(cta_threads<TN, GROUPS>() / 32) * 2 * kUnpackHalfWords);
   }
   if (tid == 0) GNC_T(7, 3, gtimer());  // CTA exit
 }

@@ -228,8 +228,9 @@ constexpr int kUnpackWarps = 8;
 __global__ void __launch_bounds__(kUnpackWarps * 32) fleet_unpack_kernel(
     const uint32_t* slots, const unsigned long long* flags, unsigned long long epoch, int world, int rank, uint32_t slot_u32, uint32_t cap,
     uint32_t* out_idx, uint32_t out_cap, int64_t* out_counts, unsigned int* done, AckPtrs ack_peer) {
-  __shared__ uint32_t buf[kUnpackWarps * 1024];
+  __shared__ __align__(16) uint32_t buf[kUnpackWarps * 2 * gnc::kUnpackHalfWords];
   __shared__ unsigned long long sh[64];
+  __shared__ uint32_t lut[256];
   gnc::FleetUnpack u;
   u.slots = slots;
   u.flags = flags;
@@ -245,7 +246,7 @@ __global__ void __launch_bounds__(kUnpackWarps * 32) fleet_unpack_kernel(
   u.ack_peer = ack_peer.p;
   u.timing = reinterpret_cast<unsigned long long*>(done) + 8;
   u.t_before = 0;
-  gnc::fleet_unpack(u, buf, sh);
+  gnc::fleet_unpack(u, buf, sh, lut);
 }
 
 }  // namespace

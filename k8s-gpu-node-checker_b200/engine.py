@@ -200,7 +200,7 @@ class Classifier:
         self._check(self.lib.gnc_fleet_timing(self._h, t))
         k = max(1, int(t[3]))
         return {"wait_us": t[0] / k / 1e3, "rebuild_us": t[1] / k / 1e3, "rebuild_us_max": t[2] / 1e3, "ctas": int(t[3]),
-                "classify_us": t[4] / k / 1e3}
+                "classify_us": t[4] / k / 1e3, "rebuild_header_us": t[5] / k / 1e3, "rebuild_groups_us": t[6] / k / 1e3}
 
     def gather(self, local: DeviceResult, fleet: DeviceResult, stream: Optional[torch.cuda.Stream] = None) -> DeviceResult:
         s = stream or torch.cuda.current_stream(self.device)
