@@ -688,7 +688,7 @@ def run_b200(args):
             line["json"] = run_json_leg(args, torch, engine, synth, clf, dev, truth, peak, peak_src)
         if args.seam_nodes > 0:
             line["e2e_seam"] = run_seam_leg(args, synth, clf)
-    if args.cpu_sample > 0:
+    if args.cpu_sample > 0 and world == 1:          # the CPU baseline is taken on rank 0 at N = 1 only
         kind, rate, dt, g, r = cpu_rate(args.cpu_sample)
         cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": kind,
                "sample": f"first {args.cpu_sample} nodes of the same fleet, {dt:.1f} s, python {sys.version.split()[0]}, "
